@@ -1,0 +1,453 @@
+// C ABI of libcpnb200.so (see include/cpn_b200.h). Host side only: argument checks, TMA descriptor encoding,
+// kernel selection and launch, and the plan recorder. No torch types, no allocation of user-visible memory.
+#include "../../include/cpn_b200.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "convnext_kernels.cuh"
+#include "gemm_tcgen05.cuh"
+#include "head_kernels.cuh"
+#include "layout_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return -1;
+}
+
+#define CPN_CUDA(expr)                                                                           \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess) return fail("%s: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+using Launch = std::function<int(cudaStream_t)>;
+
+int submit(cpn_plan* plan, void* stream, Launch fn);
+
+// ------------------------------------------------------------------------------------------------ TMA descriptors
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// bf16 row-major [rows, K] matrix, box = 64 (K) x box_rows, 128-byte swizzle; out-of-bounds reads give zeros.
+int make_tmap(CUtensorMap* m, const void* ptr, long long rows, int K, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA operand not 16-byte aligned");
+    if (K % 8 != 0) return fail("TMA operand row pitch must be a multiple of 16 bytes (K %% 8 == 0), K=%d", K);
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(K) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(cpn::GEMM_BK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld K=%d box_rows=%d)",
+                                       static_cast<int>(r), rows, K, box_rows);
+    return 0;
+}
+
+int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------------ GEMM dispatch
+struct GemmLaunch {
+    CUtensorMap ta, tb, ta_lo, tb_lo;
+    cpn::GemmParams p;
+    int grid;
+};
+
+template <int BN, int ACT, bool SPLIT>
+int launch_gemm_inst(const GemmLaunch& g, cudaStream_t st) {
+    using S = cpn::GemmSmem<BN, SPLIT>;
+    auto kern = cpn::gemm_bf16_tcgen05_kernel<BN, ACT, SPLIT>;
+    static bool attr_done = false;  // per instantiation
+    if (!attr_done) {
+        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        attr_done = true;
+    }
+    kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.ta_lo, g.tb_lo, g.p);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int BN, bool SPLIT>
+int launch_gemm_act(const GemmLaunch& g, int act, cudaStream_t st) {
+    switch (act) {
+        case CPN_ACT_NONE: return launch_gemm_inst<BN, cpn::ACT_NONE, SPLIT>(g, st);
+        case CPN_ACT_GELU: return launch_gemm_inst<BN, cpn::ACT_GELU, SPLIT>(g, st);
+        case CPN_ACT_RELU: return launch_gemm_inst<BN, cpn::ACT_RELU, SPLIT>(g, st);
+    }
+    return fail("unknown activation %d", act);
+}
+
+template <bool SPLIT>
+int launch_gemm_bn(const GemmLaunch& g, int bn, int act, cudaStream_t st) {
+    switch (bn) {
+        case 32: return launch_gemm_act<32, SPLIT>(g, act, st);
+        case 64: return launch_gemm_act<64, SPLIT>(g, act, st);
+        case 96: return launch_gemm_act<96, SPLIT>(g, act, st);
+        case 128: return launch_gemm_act<128, SPLIT>(g, act, st);
+        case 192: return launch_gemm_act<192, SPLIT>(g, act, st);
+        case 256: return launch_gemm_act<256, SPLIT>(g, act, st);
+    }
+    return fail("no GEMM instantiation for BN=%d", bn);
+}
+
+// Largest tile width that divides N; fall back to narrower tiles when the grid would not fill the SMs.
+int pick_bn(int M, int N, bool split) {
+    static const int cands[] = {256, 192, 128, 96, 64, 32};
+    const int m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
+    int best = 0;
+    for (int bn : cands) {
+        if (N % bn != 0) continue;
+        if (split && bn > 128) continue;  // hi+lo planes double the stage size
+        if (best == 0) best = bn;
+        if (m_blocks * (N / bn) >= num_sms()) return bn;  // first (largest) width with at least one full wave
+    }
+    // no width fills the machine: take the narrowest divisor >= 64 for more CTAs
+    for (int i = 5; i >= 0; --i) {
+        const int bn = cands[i];
+        if (N % bn == 0 && bn >= 64 && !(split && bn > 128)) return bn;
+    }
+    return best;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ plan
+struct cpn_plan {
+    std::vector<Launch> ops;
+};
+
+namespace {
+int submit(cpn_plan* plan, void* stream, Launch fn) {
+    if (plan != nullptr) {
+        plan->ops.push_back(std::move(fn));
+        return 0;
+    }
+    return fn(static_cast<cudaStream_t>(stream));
+}
+}  // namespace
+
+extern "C" {
+
+int cpn_version(void) { return 100; }
+
+const char* cpn_last_error(void) { return g_err.c_str(); }
+
+int cpn_check_device(void) {
+    int dev = 0;
+    CPN_CUDA(cudaGetDevice(&dev));
+    int major = 0, minor = 0;
+    CPN_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    CPN_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev));
+    if (major != 10) return fail("libcpnb200 is built for sm_100a only; device %d is sm_%d%d", dev, major, minor);
+    if (get_encode_fn() == nullptr) return fail("driver does not export cuTensorMapEncodeTiled");
+    return 0;
+}
+
+int cpn_plan_create(cpn_plan** out) {
+    if (out == nullptr) return fail("cpn_plan_create: null output");
+    *out = new cpn_plan();
+    return 0;
+}
+
+int cpn_plan_run(cpn_plan* plan, void* stream) {
+    if (plan == nullptr) return fail("cpn_plan_run: null plan");
+    for (auto& op : plan->ops) {
+        const int rc = op(static_cast<cudaStream_t>(stream));
+        if (rc != 0) return rc;
+    }
+    return 0;
+}
+
+int cpn_plan_num_ops(const cpn_plan* plan) { return plan == nullptr ? -1 : static_cast<int>(plan->ops.size()); }
+
+int cpn_plan_destroy(cpn_plan* plan) {
+    delete plan;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ ConvNeXt ops
+int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bias, const float* ln_w,
+                const float* ln_b, float* out, int B, int H, int W, float eps, void* stream) {
+    if (B <= 0 || H < 4 || W < 4) return fail("cpn_stem_ln: bad shape B=%d H=%d W=%d", B, H, W);
+    const int Ho = (H - 4) / 4 + 1, Wo = (W - 4) / 4 + 1;
+    const long long groups = static_cast<long long>(B) * Ho * ((Wo + cpn::STEM_TOK - 1) / cpn::STEM_TOK);
+    long long blocks = (groups + cpn::STEM_WARPS - 1) / cpn::STEM_WARPS;
+    const long long cap = static_cast<long long>(num_sms()) * 2;  // weights live in registers: keep CTAs persistent
+    if (blocks > cap) blocks = cap;
+    const int grid = static_cast<int>(blocks);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::stem_ln_kernel<<<grid, cpn::STEM_WARPS * 32, 0, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float* bias, const float* ln_w,
+                   const float* ln_b, void* out_hi, void* out_lo, int B, int H, int W, int C, float eps,
+                   void* stream) {
+    if (C % 2 != 0 || C > 2 * 32 * cpn::DW_MAX_WARPS) return fail("cpn_dwconv7_ln: unsupported C=%d", C);
+    if (B <= 0 || B > 65535) return fail("cpn_dwconv7_ln: unsupported B=%d", B);
+    const int threads = ((C / 2 + 31) / 32) * 32;
+    const int tw = (threads > 192) ? 2 : 4;
+    // rows per CTA: whole column strips when the batch already fills the machine, shorter segments otherwise
+    const int strips = (W + tw - 1) / tw;
+    int rows = H;
+    while (rows > 8 && static_cast<long long>(B) * strips * ((H + rows - 1) / rows) < 2LL * num_sms()) rows = (rows + 1) / 2;
+    const dim3 grid(strips, (H + rows - 1) / rows, B);
+    auto* hi = static_cast<__nv_bfloat16*>(out_hi);
+    auto* lo = static_cast<__nv_bfloat16*>(out_lo);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        if (tw == 2)
+            cpn::dwconv7_ln_kernel<2><<<grid, threads, 0, st>>>(x, w49, bias, ln_w, ln_b, hi, lo, H, W, C, rows, eps);
+        else
+            cpn::dwconv7_ln_kernel<4><<<grid, threads, 0, st>>>(x, w49, bias, ln_w, ln_b, hi, lo, H, W, C, rows, eps);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const float* ln_b, void* out_hi, void* out_lo,
+                   int B, int H, int W, int C, int stride, float eps, void* stream) {
+    if (C % 32 != 0 || C > 32 * cpn::LN_MAX_PER_LANE) return fail("cpn_ln_im2col2: unsupported C=%d", C);
+    if (stride != 1 && stride != 2) return fail("cpn_ln_im2col2: stride must be 1 or 2");
+    if (H < 2 || W < 2) return fail("cpn_ln_im2col2: map too small");
+    const int Ho = (H - 2) / stride + 1, Wo = (W - 2) / stride + 1;
+    const long long ntok = static_cast<long long>(B) * H * W;
+    const int grid = static_cast<int>((ntok + 7) / 8);
+    auto* hi = static_cast<__nv_bfloat16*>(out_hi);
+    auto* lo = static_cast<__nv_bfloat16*>(out_lo);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::ln_im2col2_kernel<<<grid, 256, 0, st>>>(x, ln_w, ln_b, hi, lo, B, H, W, C, stride, Ho, Wo, eps);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* Bw, const void* Bw_lo, int M, int N,
+                  int K, const float* bias, const float* scale, const float* res_f32, const void* res_bf16,
+                  float* out_f32, void* out_bf16, void* out_bf16_lo, int act, int relu_after_res, void* stream) {
+    if (M <= 0 || N <= 0 || K <= 0) return fail("cpn_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+    if (N % 32 != 0) return fail("cpn_gemm_bf16: N must be a multiple of 32, N=%d", N);
+    if (K % 8 != 0) return fail("cpn_gemm_bf16: K must be a multiple of 8, K=%d", K);
+    if ((A_lo == nullptr) != (Bw_lo == nullptr)) return fail("cpn_gemm_bf16: A_lo and Bw_lo must both be given");
+    if (out_f32 == nullptr && out_bf16 == nullptr) return fail("cpn_gemm_bf16: no output");
+    if (out_bf16_lo != nullptr && out_bf16 == nullptr) return fail("cpn_gemm_bf16: lo plane needs the hi plane");
+    const bool split = A_lo != nullptr;
+    const int bn = pick_bn(M, N, split);
+    if (bn == 0) return fail("cpn_gemm_bf16: no tile width divides N=%d", N);
+    GemmLaunch g;
+    memset(&g, 0, sizeof(g));
+    if (make_tmap(&g.ta, A, M, K, cpn::GEMM_BM) != 0) return -1;
+    if (make_tmap(&g.tb, Bw, N, K, bn) != 0) return -1;
+    if (split) {
+        if (make_tmap(&g.ta_lo, A_lo, M, K, cpn::GEMM_BM) != 0) return -1;
+        if (make_tmap(&g.tb_lo, Bw_lo, N, K, bn) != 0) return -1;
+    } else {
+        g.ta_lo = g.ta;
+        g.tb_lo = g.tb;
+    }
+    g.p.M = M; g.p.N = N; g.p.K = K;
+    g.p.num_m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
+    g.p.num_n_blocks = N / bn;
+    g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+    g.p.bias = bias; g.p.scale = scale; g.p.res_f32 = res_f32;
+    g.p.res_bf16 = static_cast<const __nv_bfloat16*>(res_bf16);
+    g.p.out_f32 = out_f32;
+    g.p.out_bf16 = static_cast<__nv_bfloat16*>(out_bf16);
+    g.p.out_bf16_lo = static_cast<__nv_bfloat16*>(out_bf16_lo);
+    g.p.relu_after_res = relu_after_res;
+    const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
+    g.grid = tiles < num_sms() ? tiles : num_sms();
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        return split ? launch_gemm_bn<true>(g, bn, act, st) : launch_gemm_bn<false>(g, bn, act, st);
+    });
+}
+
+// ------------------------------------------------------------------------------------------------ head ops
+int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const float* bias, float* z, long long T,
+                      int C, int P, void* stream) {
+    const size_t smem = static_cast<size_t>(P) * C * sizeof(float);
+    if (smem > 200 * 1024) return fail("cpn_addon_conv1x1: P*C=%d*%d too large for the small-P kernel", P, C);
+    long long blocks = (T + 7) / 8;
+    if (blocks > 4LL * num_sms()) blocks = 4LL * num_sms();
+    const int grid = static_cast<int>(blocks);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        if (smem > 48 * 1024)
+            CPN_CUDA(cudaFuncSetAttribute(cpn::addon_conv1x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(smem)));
+        cpn::addon_conv1x1_kernel<<<grid, 256, smem, st>>>(feat, w, bias, z, T, C, P);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
+                     float* partial, int B, int HW, int P, int chunks, void* stream) {
+    if (chunks <= 0 || B <= 0 || B > 65535) return fail("cpn_softmax_pool: bad chunks/B");
+    const size_t smem = 8 * static_cast<size_t>(P) * sizeof(float);
+    if (smem > 200 * 1024) return fail("cpn_softmax_pool: P=%d too large", P);
+    const dim3 grid(chunks, B);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        if (smem > 48 * 1024)
+            CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(smem)));
+        cpn::softmax_pool_kernel<<<grid, 256, smem, st>>>(z, gumbel, tau, hard, mode, map, partial, HW, P, chunks);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, int inference, int use_ste,
+                  int max_count, int encoding, const float* enc_w0, const float* enc_w1, const float* enc_w2,
+                  const float* cls_w, const float* cls_b, float* pooled_out, float* logits_out, int B, int P, int D,
+                  int K, void* stream) {
+    cpn::TailParams tp;
+    tp.partial = partial; tp.chunks = chunks; tp.mode = mode; tp.inference = inference; tp.use_ste = use_ste;
+    tp.max_count = max_count; tp.encoding = encoding; tp.enc_w0 = enc_w0; tp.enc_w1 = enc_w1; tp.enc_w2 = enc_w2;
+    tp.cls_w = cls_w; tp.cls_b = cls_b; tp.pooled_out = pooled_out; tp.logits_out = logits_out;
+    tp.P = P; tp.D = D; tp.K = K;
+    if (mode == CPN_POOL_SUM) {
+        if (max_count <= 0) return fail("cpn_head_tail: max_count must be positive");
+        if ((encoding == CPN_ENC_ONEHOT || encoding == CPN_ENC_LINEAR) && D % P != 0)
+            return fail("cpn_head_tail: D=%d not a multiple of P=%d", D, P);
+        if ((encoding == CPN_ENC_LINEAR || encoding == CPN_ENC_LINEAR_FULL || encoding == CPN_ENC_BILINEAR) &&
+            enc_w0 == nullptr)
+            return fail("cpn_head_tail: encoding %d needs weights", encoding);
+        if (encoding == CPN_ENC_BILINEAR && (enc_w1 == nullptr || enc_w2 == nullptr))
+            return fail("cpn_head_tail: bilinear needs W and V");
+        if ((encoding == CPN_ENC_IDENTITY || encoding == CPN_ENC_NONE) && D != P)
+            return fail("cpn_head_tail: identity encoding needs D == P");
+    } else if (D != P) {
+        return fail("cpn_head_tail: max pooling needs D == P");
+    }
+    const size_t smem = (static_cast<size_t>(P) + 2 * static_cast<size_t>(D)) * sizeof(float);
+    if (smem > 200 * 1024) return fail("cpn_head_tail: P=%d D=%d too large", P, D);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        if (smem > 48 * 1024)
+            CPN_CUDA(cudaFuncSetAttribute(cpn::head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(smem)));
+        cpn::head_tail_kernel<<<B, 256, smem, st>>>(tp);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+// ------------------------------------------------------------------------------------------------ layout / ResNet helpers
+int cpn_nhwc_to_nchw(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream) {
+    const dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::transpose_last2_kernel<<<grid, 256, 0, st>>>(x, out, HW, C);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream) {
+    const dim3 grid((C + 31) / 32, (HW + 31) / 32, B);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::transpose_last2_kernel<<<grid, 256, 0, st>>>(x, out, C, HW);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+static int gather_grid(long long total) {
+    long long blocks = (total + 255) / 256;
+    const long long cap = 16LL * num_sms();
+    return static_cast<int>(blocks > cap ? cap : (blocks < 1 ? 1 : blocks));
+}
+
+int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, int k, int stride,
+                    int pad, int Kpad, void* stream) {
+    if (C % 8 != 0 || Kpad % 8 != 0 || Kpad < k * k * C) return fail("cpn_im2col_bf16: bad C=%d Kpad=%d", C, Kpad);
+    const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (Kpad / 8));
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::im2col_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H, W, C,
+                                                      k, stride, pad, Ho, Wo, Kpad);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, int B, int C, int H, int W, int k, int stride,
+                        int pad, int Kpad, void* stream) {
+    if (Kpad < k * k * C) return fail("cpn_im2col_nchw_f32: Kpad too small");
+    const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * Kpad);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::im2col_nchw_f32_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(out), B, C, H, W, k, stride,
+                                                          pad, Ho, Wo, Kpad);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream) {
+    if (C % 8 != 0) return fail("cpn_maxpool3s2_bf16: C must be a multiple of 8");
+    const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (C / 8));
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::maxpool3s2_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H,
+                                                          W, C, Ho, Wo);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream) {
+    if (C % 8 != 0) return fail("cpn_subsample2_bf16: C must be a multiple of 8");
+    const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (C / 8));
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::subsample2_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H,
+                                                          W, C, Ho, Wo);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+}  // extern "C"

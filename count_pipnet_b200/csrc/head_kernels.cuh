@@ -1,0 +1,215 @@
+// Prototype head of PIP-Net / Count-PIP-Net on channels-last features.
+//   addon_conv1x1_kernel   optional 1x1 add-on conv C -> P (+bias)                     pipnet/pipnet.py:102, count_pipnet.py:378
+//   softmax_pool_kernel    per-patch softmax over P (or hard Gumbel-softmax), then the spatial max (PIP-Net,
+//                          pipnet/pipnet.py:96-108) or spatial sum (Count-PIP-Net, count_pipnet.py:88) as per-chunk partials;
+//                          the patch x prototype map is written (NCHW) only when the caller passes a buffer
+//   head_tail_kernel       chunk reduction, inference threshold (pipnet.py:36) or round/clamp (count_pipnet.py:90-97),
+//                          count encoding (count_pipnet_utils.py:141-185, 371-385, 429-439, 461-462, 498-519) and the
+//                          ReLU-weight classifier (pipnet.py:71)
+#pragma once
+#include "convnext_kernels.cuh"
+
+namespace cpn {
+
+// ------------------------------------------------------------------------------------------------ add-on conv
+// Warp per patch token, lanes split the C input channels, weights [P][C] staged in shared memory.
+__global__ void __launch_bounds__(256)
+addon_conv1x1_kernel(const float* __restrict__ feat, const float* __restrict__ w, const float* __restrict__ bias,
+                     float* __restrict__ z, long long T, int C, int P) {
+    extern __shared__ float s_w[];  // [P][C]
+    for (int i = threadIdx.x; i < P * C; i += blockDim.x) s_w[i] = w[i];
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (long long t = static_cast<long long>(blockIdx.x) * wpb + warp; t < T; t += static_cast<long long>(gridDim.x) * wpb) {
+        const float* f = feat + t * C;
+        for (int p = 0; p < P; ++p) {
+            float a = 0.f;
+            for (int c = lane; c < C; c += 32) a = fmaf(__ldg(f + c), s_w[p * C + c], a);
+            a = warp_sum(a);
+            if (lane == 0) z[t * P + p] = a + (bias != nullptr ? bias[p] : 0.f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ softmax + pool
+enum PoolMode : int { POOL_MAX = 0, POOL_SUM = 1 };
+
+// grid = (chunks, B); each CTA owns a contiguous range of one image's patch tokens, one warp per token at a time.
+// z:       [B, HW, P] fp32 logits (token-major)
+// gumbel:  [B, P, H*W] fp32 noise in the reference's NCHW layout, or null
+// map:     [B, P, H*W] fp32 output (NCHW like the reference's proto_features), or null
+// partial: [B, chunks, P]
+__global__ void __launch_bounds__(256)
+softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbel, float tau, int hard, int mode,
+                    float* __restrict__ map, float* __restrict__ partial, int HW, int P, int chunks) {
+    extern __shared__ float s_pool[];  // [warps][P]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const int b = blockIdx.y;
+    const int chunk = blockIdx.x;
+    const int per_chunk = (HW + chunks - 1) / chunks;
+    const int t0 = chunk * per_chunk;
+    const int t1 = min(HW, t0 + per_chunk);
+    float* my_pool = s_pool + warp * P;
+    for (int p = lane; p < P; p += 32) my_pool[p] = 0.f;  // probabilities are >= 0, so 0 is neutral for max and sum
+    __syncwarp();
+    for (int t = t0 + warp; t < t1; t += wpb) {
+        const float* zr = z + (static_cast<size_t>(b) * HW + t) * P;
+        const float* gr = gumbel != nullptr ? gumbel + static_cast<size_t>(b) * P * HW + t : nullptr;
+        // pass 1: row max (and arg-max, first index on ties)
+        float m = -INFINITY;
+        int am = 0x7fffffff;
+        for (int p = lane; p < P; p += 32) {
+            float v = __ldg(zr + p);
+            if (gr != nullptr) v = (v + __ldg(gr + static_cast<size_t>(p) * HW)) / tau;
+            if (v > m) { m = v; am = p; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, m, o);
+            const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+            if (om > m || (om == m && oa < am)) { m = om; am = oa; }
+        }
+        // pass 2: sum of exponentials
+        float s = 0.f;
+        for (int p = lane; p < P; p += 32) {
+            float v = __ldg(zr + p);
+            if (gr != nullptr) v = (v + __ldg(gr + static_cast<size_t>(p) * HW)) / tau;
+            s += expf(v - m);
+        }
+        s = warp_sum(s);
+        const float inv_s = 1.0f / s;
+        // pass 3: probabilities -> pool (+ optional map)
+        for (int p = lane; p < P; p += 32) {
+            float v = __ldg(zr + p);
+            if (gr != nullptr) v = (v + __ldg(gr + static_cast<size_t>(p) * HW)) / tau;
+            float y = expf(v - m) * inv_s;
+            if (hard) y = ((p == am ? 1.0f : 0.0f) - y) + y;  // y_hard - y_soft + y_soft (straight-through form)
+            if (mode == POOL_MAX) my_pool[p] = fmaxf(my_pool[p], y);
+            else my_pool[p] += y;
+            if (map != nullptr) map[(static_cast<size_t>(b) * P + p) * HW + t] = y;
+        }
+    }
+    __syncthreads();
+    float* out = partial + (static_cast<size_t>(b) * chunks + chunk) * P;
+    for (int p = threadIdx.x; p < P; p += blockDim.x) {
+        float a = s_pool[p];
+        for (int wv = 1; wv < wpb; ++wv) {
+            const float o = s_pool[wv * P + p];
+            a = (mode == POOL_MAX) ? fmaxf(a, o) : a + o;
+        }
+        out[p] = a;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ tail
+enum Encoding : int { ENC_NONE = 0, ENC_ONEHOT = 1, ENC_LINEAR = 2, ENC_LINEAR_FULL = 3, ENC_BILINEAR = 4, ENC_IDENTITY = 5 };
+
+struct TailParams {
+    const float* partial;  // [B, chunks, P]
+    int chunks;
+    int mode;        // PoolMode
+    int inference;   // forward(xs, inference)
+    int use_ste;     // CountPIPNet._use_ste
+    int max_count;
+    int encoding;    // Encoding
+    const float* enc_w0;  // linear: [E,1]; linear_full: [D,P]; bilinear: embed [D,P]
+    const float* enc_w1;  // bilinear: W [D,D]
+    const float* enc_w2;  // bilinear: V [D,D]
+    const float* cls_w;   // [K, D]
+    const float* cls_b;   // [K] or null
+    float* pooled_out;    // [B, P]
+    float* logits_out;    // [B, K]
+    int P, D, K;
+};
+
+// One CTA per image. Shared memory: pooled[P] | inter[D] | tmp[D]
+__global__ void __launch_bounds__(256)
+head_tail_kernel(const TailParams p) {
+    extern __shared__ float s_buf[];
+    float* s_pooled = s_buf;
+    float* s_inter = s_buf + p.P;
+    float* s_tmp = s_inter + p.D;
+    const int b = blockIdx.x;
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31, wpb = blockDim.x >> 5;
+    const int M = p.max_count;
+
+    for (int i = tid; i < p.P; i += blockDim.x) {
+        const float* pp = p.partial + static_cast<size_t>(b) * p.chunks * p.P + i;
+        float a = pp[0];
+        for (int c = 1; c < p.chunks; ++c) {
+            const float o = pp[static_cast<size_t>(c) * p.P];
+            a = (p.mode == POOL_MAX) ? fmaxf(a, o) : a + o;
+        }
+        float ret;
+        if (p.mode == POOL_MAX) {
+            if (p.inference) a = (a < 0.1f) ? 0.f : a;
+            ret = a;
+        } else {
+            const float counts = a;
+            if (p.use_ste || p.inference) a = rintf(a);  // torch.round: half to even
+            a = fminf(fmaxf(a, 0.f), static_cast<float>(M));
+            ret = p.inference ? a : counts;
+        }
+        s_pooled[i] = a;
+        p.pooled_out[static_cast<size_t>(b) * p.P + i] = ret;
+    }
+    __syncthreads();
+
+    // count encoding -> s_inter[D]
+    if (p.mode == POOL_MAX || p.encoding == ENC_IDENTITY || p.encoding == ENC_NONE) {
+        for (int i = tid; i < p.D; i += blockDim.x) s_inter[i] = s_pooled[i];
+    } else if (p.encoding == ENC_ONEHOT) {
+        for (int i = tid; i < p.D; i += blockDim.x) {
+            const int proto = i / M, bin = i % M;
+            float x = s_pooled[proto];
+            if (p.use_ste) x = rintf(x);
+            float e = 0.f;
+            if (x > 0.1f) {
+                long long idx = static_cast<long long>(x) - 1;
+                idx = idx < 0 ? 0 : (idx > M - 1 ? M - 1 : idx);
+                e = (bin == static_cast<int>(idx)) ? 1.f : 0.f;
+            }
+            s_inter[i] = e;
+        }
+    } else if (p.encoding == ENC_LINEAR) {
+        const int E = p.D / p.P;
+        for (int i = tid; i < p.D; i += blockDim.x) s_inter[i] = s_pooled[i / E] * p.enc_w0[i % E];
+    } else if (p.encoding == ENC_LINEAR_FULL || p.encoding == ENC_BILINEAR) {
+        float* dst = (p.encoding == ENC_BILINEAR) ? s_tmp : s_inter;
+        for (int i = warp; i < p.D; i += wpb) {
+            float a = 0.f;
+            for (int j = lane; j < p.P; j += 32) a = fmaf(s_pooled[j], p.enc_w0[static_cast<size_t>(i) * p.P + j], a);
+            a = warp_sum(a);
+            if (lane == 0) dst[i] = a;
+        }
+        if (p.encoding == ENC_BILINEAR) {
+            __syncthreads();
+            for (int i = warp; i < p.D; i += wpb) {
+                float a = 0.f, c = 0.f;
+                for (int j = lane; j < p.D; j += 32) {
+                    const float e = s_tmp[j];
+                    a = fmaf(e, p.enc_w1[static_cast<size_t>(i) * p.D + j], a);
+                    c = fmaf(e, p.enc_w2[static_cast<size_t>(i) * p.D + j], c);
+                }
+                a = warp_sum(a);
+                c = warp_sum(c);
+                if (lane == 0) s_inter[i] = a * c;
+            }
+        }
+    }
+    __syncthreads();
+
+    // non-negative classifier: logits[k] = sum_d relu(W[k,d]) * inter[d] + bias[k]
+    for (int k = warp; k < p.K; k += wpb) {
+        const float* wr = p.cls_w + static_cast<size_t>(k) * p.D;
+        float a = 0.f;
+        for (int d = lane; d < p.D; d += 32) a = fmaf(s_inter[d], fmaxf(__ldg(wr + d), 0.f), a);
+        a = warp_sum(a);
+        if (lane == 0) p.logits_out[static_cast<size_t>(b) * p.K + k] = a + (p.cls_b != nullptr ? p.cls_b[k] : 0.f);
+    }
+}
+
+}  // namespace cpn

@@ -1,0 +1,134 @@
+// Layout / gather kernels: NCHW<->NHWC transposes at the module boundary, and the im2col / pooling / subsample
+// gathers that turn the ResNet convolutions of features/resnet_features.py into rows for the tcgen05 GEMM.
+#pragma once
+#include "ptx.cuh"
+
+namespace cpn {
+
+// [B, HW, C] -> [B, C, HW] (and back) through a 32x33 shared-memory tile; grid = (ceil(HW/32), ceil(C/32), B).
+__global__ void __launch_bounds__(256)
+transpose_last2_kernel(const float* __restrict__ in, float* __restrict__ out, int R, int Ccols) {
+    // in: [B, R, Ccols], out: [B, Ccols, R]
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z;
+    const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    const float* ib = in + static_cast<size_t>(b) * R * Ccols;
+    float* ob = out + static_cast<size_t>(b) * R * Ccols;
+    for (int i = ty; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + tx;
+        tile[i][tx] = (r < R && c < Ccols) ? ib[static_cast<size_t>(r) * Ccols + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + tx;
+        if (r < R && c < Ccols) ob[static_cast<size_t>(c) * R + r] = tile[tx][i];
+    }
+}
+
+// im2col over a channels-last bf16 map, 8 channels (16 B) per thread.
+__global__ void __launch_bounds__(256)
+im2col_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int k, int stride,
+                   int pad, int Ho, int Wo, int Kpad) {
+    const int c8 = C >> 3, k8 = Kpad >> 3;
+    const long long total = static_cast<long long>(B) * Ho * Wo * k8;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int col = static_cast<int>(i % k8);
+        const long long row = i / k8;
+        const int wo = static_cast<int>(row % Wo);
+        const int ho = static_cast<int>((row / Wo) % Ho);
+        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        const int tap = col / c8, cc = col % c8;
+        if (tap < k * k) {
+            const int kh = tap / k, kw = tap % k;
+            const int hi = ho * stride - pad + kh, wi = wo * stride - pad + kw;
+            if (hi >= 0 && hi < H && wi >= 0 && wi < W)
+                v = __ldg(x + ((static_cast<size_t>(b) * H + hi) * W + wi) * c8 + cc);
+        }
+        out[i] = v;
+    }
+}
+
+// im2col straight from the fp32 NCHW network input; column = c*k*k + kh*k + kw (the torch weight flattening).
+__global__ void __launch_bounds__(256)
+im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int C, int H, int W, int k,
+                       int stride, int pad, int Ho, int Wo, int Kpad) {
+    const long long total = static_cast<long long>(B) * Ho * Wo * Kpad;
+    const int kk = k * k;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int col = static_cast<int>(i % Kpad);
+        const long long row = i / Kpad;
+        const int wo = static_cast<int>(row % Wo);
+        const int ho = static_cast<int>((row / Wo) % Ho);
+        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
+        float v = 0.f;
+        if (col < C * kk) {
+            const int c = col / kk, r = col % kk;
+            const int kh = r / k, kw = r % k;
+            const int hi = ho * stride - pad + kh, wi = wo * stride - pad + kw;
+            if (hi >= 0 && hi < H && wi >= 0 && wi < W)
+                v = __ldg(x + ((static_cast<size_t>(b) * C + c) * H + hi) * W + wi);
+        }
+        out[i] = __float2bfloat16_rn(v);
+    }
+}
+
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+    __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a);
+    __nv_bfloat162 y = *reinterpret_cast<__nv_bfloat162*>(&b);
+    __nv_bfloat162 m = __hmax2(x, y);
+    return *reinterpret_cast<uint32_t*>(&m);
+}
+
+// MaxPool2d(kernel 3, stride 2, pad 1), channels-last bf16, 8 channels per thread.
+__global__ void __launch_bounds__(256)
+maxpool3s2_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
+    const int c8 = C >> 3;
+    const long long total = static_cast<long long>(B) * Ho * Wo * c8;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int cc = static_cast<int>(i % c8);
+        const long long row = i / c8;
+        const int wo = static_cast<int>(row % Wo);
+        const int ho = static_cast<int>((row / Wo) % Ho);
+        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
+        bool first = true;
+        uint4 m = make_uint4(0u, 0u, 0u, 0u);
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * 2 - 1 + kh;
+            if (hi < 0 || hi >= H) continue;
+            for (int kw = 0; kw < 3; ++kw) {
+                const int wi = wo * 2 - 1 + kw;
+                if (wi < 0 || wi >= W) continue;
+                const uint4 v = __ldg(x + ((static_cast<size_t>(b) * H + hi) * W + wi) * c8 + cc);
+                if (first) { m = v; first = false; }
+                else {
+                    m.x = bf16x2_max(m.x, v.x); m.y = bf16x2_max(m.y, v.y);
+                    m.z = bf16x2_max(m.z, v.z); m.w = bf16x2_max(m.w, v.w);
+                }
+            }
+        }
+        out[i] = m;
+    }
+}
+
+// out[b, ho, wo, :] = x[b, 2*ho, 2*wo, :]
+__global__ void __launch_bounds__(256)
+subsample2_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
+    const int c8 = C >> 3;
+    const long long total = static_cast<long long>(B) * Ho * Wo * c8;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int cc = static_cast<int>(i % c8);
+        const long long row = i / c8;
+        const int wo = static_cast<int>(row % Wo);
+        const int ho = static_cast<int>((row / Wo) % Ho);
+        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
+        out[i] = __ldg(x + ((static_cast<size_t>(b) * H + 2 * ho) * W + 2 * wo) * c8 + cc);
+    }
+}
+
+}  // namespace cpn

@@ -1,0 +1,141 @@
+"""Tensor-level wrappers over the C ABI (one function per entry point of include/cpn_b200.h).
+
+Every function takes CUDA tensors that already have the layout the kernel wants, enqueues the kernel on torch's
+current stream (or records it into `plan`) and returns nothing: outputs are caller-allocated. These wrappers do the
+shape bookkeeping only; there is no torch arithmetic here and no fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ptr
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.CpnError("count_pipnet_b200 kernels need CUDA tensors; there is no CPU fallback")
+        if t is not None and not t.is_contiguous():
+            raise _lib.CpnError("count_pipnet_b200 kernels need contiguous tensors")
+
+
+class Plan:
+    """A recorded launch sequence (cpn_plan). Tensors referenced by recorded ops must outlive the plan."""
+
+    def __init__(self):
+        h = C.c_void_p()
+        _lib.check(_lib.load().cpn_plan_create(C.byref(h)))
+        self.handle = h
+        self.keepalive = []
+
+    def run(self) -> None:
+        _lib.check(_lib.load().cpn_plan_run(self.handle, _stream()))
+
+    def __len__(self) -> int:
+        return _lib.load().cpn_plan_num_ops(self.handle)
+
+    def __del__(self):
+        try:
+            if self.handle:
+                _lib.load().cpn_plan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+def _ph(plan):
+    return None if plan is None else plan.handle
+
+
+def check_device() -> None:
+    _lib.check(_lib.load().cpn_check_device())
+
+
+def stem_ln(x, w, b, ln_w, ln_b, out, eps=1e-6, plan=None):
+    """x [B,3,H,W] fp32 -> out [B,H/4,W/4,96] fp32 (channels-last)."""
+    _need_cuda(x, w, b, ln_w, ln_b, out)
+    B, _, H, W = x.shape
+    _lib.call("cpn_stem_ln", _ph(plan), ptr(x), ptr(w), ptr(b), ptr(ln_w), ptr(ln_b), ptr(out), B, H, W, eps, _stream())
+
+
+def dwconv7_ln(x, w49, b, ln_w, ln_b, out_hi, out_lo=None, eps=1e-6, plan=None):
+    """x [B,H,W,C] fp32, w49 [49,C] -> out [B*H*W, C] bf16 (hi[, lo])."""
+    _need_cuda(x, w49, b, ln_w, ln_b, out_hi, out_lo)
+    B, H, W, Cc = x.shape
+    _lib.call("cpn_dwconv7_ln", _ph(plan), ptr(x), ptr(w49), ptr(b), ptr(ln_w), ptr(ln_b), ptr(out_hi), ptr(out_lo),
+              B, H, W, Cc, eps, _stream())
+
+
+def ln_im2col2(x, ln_w, ln_b, out_hi, out_lo=None, stride=2, eps=1e-6, plan=None):
+    """x [B,H,W,C] fp32 -> out [B*Ho*Wo, 4C] bf16."""
+    _need_cuda(x, ln_w, ln_b, out_hi, out_lo)
+    B, H, W, Cc = x.shape
+    _lib.call("cpn_ln_im2col2", _ph(plan), ptr(x), ptr(ln_w), ptr(ln_b), ptr(out_hi), ptr(out_lo), B, H, W, Cc, stride,
+              eps, _stream())
+
+
+def gemm_bf16(a, bw, M, N, K, *, a_lo=None, bw_lo=None, bias=None, scale=None, res_f32=None, res_bf16=None,
+              out_f32=None, out_bf16=None, out_bf16_lo=None, act=_lib.ACT_NONE, relu_after_res=False, plan=None):
+    """out = epilogue(a[M,K] @ bw[N,K]^T); a, bw bf16 row-major."""
+    _need_cuda(a, bw, a_lo, bw_lo, bias, scale, res_f32, res_bf16, out_f32, out_bf16, out_bf16_lo)
+    _lib.call("cpn_gemm_bf16", _ph(plan), ptr(a), ptr(a_lo), ptr(bw), ptr(bw_lo), M, N, K, ptr(bias), ptr(scale),
+              ptr(res_f32), ptr(res_bf16), ptr(out_f32), ptr(out_bf16), ptr(out_bf16_lo), int(act),
+              int(bool(relu_after_res)), _stream())
+
+
+def addon_conv1x1(feat, w, b, z, T, Cc, P, plan=None):
+    _need_cuda(feat, w, b, z)
+    _lib.call("cpn_addon_conv1x1", _ph(plan), ptr(feat), ptr(w), ptr(b), ptr(z), T, Cc, P, _stream())
+
+
+def softmax_pool(z, partial, B, HW, P, chunks, *, gumbel=None, tau=1.0, hard=False, mode=_lib.POOL_MAX, map_out=None,
+                 plan=None):
+    _need_cuda(z, partial, gumbel, map_out)
+    _lib.call("cpn_softmax_pool", _ph(plan), ptr(z), ptr(gumbel), float(tau), int(bool(hard)), int(mode), ptr(map_out),
+              ptr(partial), B, HW, P, chunks, _stream())
+
+
+def head_tail(partial, chunks, pooled_out, logits_out, cls_w, cls_b, B, P, D, K, *, mode=_lib.POOL_MAX,
+              inference=True, use_ste=False, max_count=3, encoding=_lib.ENC_NONE, enc_w0=None, enc_w1=None,
+              enc_w2=None, plan=None):
+    _need_cuda(partial, pooled_out, logits_out, cls_w, cls_b, enc_w0, enc_w1, enc_w2)
+    _lib.call("cpn_head_tail", _ph(plan), ptr(partial), chunks, int(mode), int(bool(inference)), int(bool(use_ste)),
+              int(max_count), int(encoding), ptr(enc_w0), ptr(enc_w1), ptr(enc_w2), ptr(cls_w), ptr(cls_b),
+              ptr(pooled_out), ptr(logits_out), B, P, D, K, _stream())
+
+
+def nhwc_to_nchw(x, out, B, HW, Cc, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_nhwc_to_nchw", _ph(plan), ptr(x), ptr(out), B, HW, Cc, _stream())
+
+
+def nchw_to_nhwc(x, out, B, HW, Cc, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_nchw_to_nhwc", _ph(plan), ptr(x), ptr(out), B, HW, Cc, _stream())
+
+
+def im2col_bf16(x, out, B, H, W, Cc, k, stride, pad, Kpad, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_im2col_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, k, stride, pad, Kpad, _stream())
+
+
+def im2col_nchw_f32(x, out, B, Cc, H, W, k, stride, pad, Kpad, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_im2col_nchw_f32", _ph(plan), ptr(x), ptr(out), B, Cc, H, W, k, stride, pad, Kpad, _stream())
+
+
+def maxpool3s2_bf16(x, out, B, H, W, Cc, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_maxpool3s2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())
+
+
+def subsample2_bf16(x, out, B, H, W, Cc, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_subsample2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())

@@ -1,0 +1,127 @@
+/* cpn_b200.h -- C ABI of libcpnb200.so: the B200 (sm_100a) forward hot path of PIP-Net / Count-PIP-Net.
+ *
+ * The reference (TarasKutsyk/Count_PIPNet) has no FFI: its boundary for this path is the Python nn.Module API
+ * (pipnet/pipnet.py:31-41 PIPNet.forward, pipnet/count_pipnet.py:70-110 CountPIPNet.forward). This library is what a
+ * drop-in module binds underneath that API (count_pipnet_b200/_lib.py is the ctypes binding; INTEGRATION.md shows
+ * the reference-side stub). Each entry point names the reference code whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned memory (torch storage); the library allocates nothing;
+ *   - `stream` is a cudaStream_t passed as void*; calls enqueue work and return without synchronising;
+ *   - return value 0 = ok, negative = error (cpn_last_error() gives a thread-local message);
+ *   - `plan` may be NULL (launch now) or a plan handle (record the launch, replayed by cpn_plan_run);
+ *   - activations are channels-last: a feature map is [B, H, W, C] = [tokens, C] with C contiguous;
+ *   - "bf16" buffers hold __nv_bfloat16; a non-NULL `*_lo` pointer asks for the residual plane of the bf16 hi/lo
+ *     split (x = hi + lo) used by fp32 mode (three-pass bf16 GEMM).
+ */
+#ifndef CPN_B200_H
+#define CPN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cpn_plan cpn_plan;
+
+/* activation codes for cpn_gemm_bf16 */
+#define CPN_ACT_NONE 0
+#define CPN_ACT_GELU 1 /* exact erf GELU, torchvision/models/convnext.py:56 */
+#define CPN_ACT_RELU 2
+
+/* pooling modes for cpn_softmax_pool / cpn_head_tail */
+#define CPN_POOL_MAX 0 /* PIP-Net: AdaptiveMaxPool2d((1,1)), pipnet/pipnet.py:105-108 */
+#define CPN_POOL_SUM 1 /* Count-PIP-Net: proto_features.sum(dim=(2,3)), pipnet/count_pipnet.py:88 */
+
+/* count encodings for cpn_head_tail (pipnet/count_pipnet.py:392-417) */
+#define CPN_ENC_NONE 0
+#define CPN_ENC_ONEHOT 1      /* count_pipnet_utils.py:141-185 */
+#define CPN_ENC_LINEAR 2      /* count_pipnet_utils.py:498-519 */
+#define CPN_ENC_LINEAR_FULL 3 /* count_pipnet_utils.py:429-439 */
+#define CPN_ENC_BILINEAR 4    /* count_pipnet_utils.py:371-385 */
+#define CPN_ENC_IDENTITY 5    /* count_pipnet_utils.py:461-462 */
+
+/* ---- library ---------------------------------------------------------------------------------------------- */
+int cpn_version(void);
+const char* cpn_last_error(void);
+/* 0 if the current device is sm_100 (B200) and the kernels can run on it. */
+int cpn_check_device(void);
+
+/* ---- plans: a recorded sequence of launches with pre-encoded TMA descriptors ------------------------------- */
+int cpn_plan_create(cpn_plan** out);
+int cpn_plan_run(cpn_plan* plan, void* stream);
+int cpn_plan_num_ops(const cpn_plan* plan);
+int cpn_plan_destroy(cpn_plan* plan);
+
+/* ---- ConvNeXt feature path --------------------------------------------------------------------------------- */
+/* Stem: Conv2d(3,96,k=4,s=4)+bias then LayerNorm2d(96) -- torchvision/models/convnext.py:120-131.
+ * x [B,3,H,W] fp32 NCHW; w [96,48] (= conv weight [96,3,4,4]); out [B,H/4,W/4,96] fp32 channels-last. */
+int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bias, const float* ln_w,
+                const float* ln_b, float* out, int B, int H, int W, float eps, void* stream);
+
+/* Depthwise 7x7 (pad 3) + bias, then LayerNorm(C) -- CNBlock.block[0..2], torchvision/models/convnext.py:52-54.
+ * x [B,H,W,C] fp32; w49 [49,C] fp32 (conv weight [C,1,7,7] transposed); out_hi/out_lo [B*H*W, C] bf16. */
+int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float* bias, const float* ln_w,
+                   const float* ln_b, void* out_hi, void* out_lo, int B, int H, int W, int C, float eps,
+                   void* stream);
+
+/* LayerNorm2d(C) then the im2col rows of Conv2d(C,C',k=2,stride) -- torchvision/models/convnext.py:146-150 with
+ * the stride surgery of features/convnext_features.py:5-15.
+ * x [B,H,W,C] fp32; out [B*Ho*Wo, 4*C] bf16 with column (kh*2+kw)*C + c, Ho = (H-2)/stride+1. */
+int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const float* ln_b, void* out_hi, void* out_lo,
+                   int B, int H, int W, int C, int stride, float eps, void* stream);
+
+/* tcgen05/TMA GEMM with fused epilogue:  v = A[M,K] * Bw[N,K]^T + bias;  v = act(v);  v *= scale;  v += residual;
+ * (relu_after_res: the ReLU is applied after the residual add instead);  outputs fp32 and/or bf16 (hi, lo).
+ * Replaces nn.Linear+GELU / nn.Linear*layer_scale+residual (torchvision/models/convnext.py:55-57,64-66), the 2x2
+ * downsample convs (:146-150) and conv+BatchNorm+ReLU of features/resnet_features.py:97-117.
+ * A [M,K] bf16 and Bw [N,K] bf16 row-major (K contiguous), K % 8 == 0, N % 32 == 0.
+ * A_lo / Bw_lo non-NULL selects fp32 mode: acc = A*Bw + A*Bw_lo + A_lo*Bw (three bf16 passes). */
+int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* Bw, const void* Bw_lo, int M, int N,
+                  int K, const float* bias, const float* scale, const float* res_f32, const void* res_bf16,
+                  float* out_f32, void* out_bf16, void* out_bf16_lo, int act, int relu_after_res, void* stream);
+
+/* ---- prototype head ---------------------------------------------------------------------------------------- */
+/* Add-on Conv2d(C,P,1)+bias on channels-last features -- pipnet/pipnet.py:102, pipnet/count_pipnet.py:378-379.
+ * feat [T,C] fp32; w [P,C]; bias [P] or NULL; z [T,P] fp32. */
+int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const float* bias, float* z, long long T,
+                      int C, int P, void* stream);
+
+/* Per-patch softmax over P (nn.Softmax(dim=1), pipnet/pipnet.py:96,103) or hard Gumbel-softmax with caller-supplied
+ * noise (count_pipnet_utils.py:33-38), then spatial max / sum per image as `chunks` partial results.
+ * z [B,HW,P] fp32; gumbel [B,P,HW] fp32 or NULL; map [B,P,HW] fp32 (NCHW proto_features) or NULL;
+ * partial [B,chunks,P] fp32. */
+int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
+                     float* partial, int B, int HW, int P, int chunks, void* stream);
+
+/* Chunk reduction, inference threshold (pipnet/pipnet.py:36) or round+clamp (pipnet/count_pipnet.py:90-97),
+ * count encoding, and the non-negative classifier F.linear(x, relu(W), b) (pipnet/pipnet.py:70-71).
+ * pooled_out [B,P] is the module's second return value; logits_out [B,K] the third. */
+int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, int inference, int use_ste,
+                  int max_count, int encoding, const float* enc_w0, const float* enc_w1, const float* enc_w2,
+                  const float* cls_w, const float* cls_b, float* pooled_out, float* logits_out, int B, int P, int D,
+                  int K, void* stream);
+
+/* ---- layout / ResNet helpers ------------------------------------------------------------------------------- */
+/* [B,H,W,C] fp32 channels-last -> [B,C,H,W] fp32 (what reference callers of net._net(x) expect). */
+int cpn_nhwc_to_nchw(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream);
+/* [B,C,H,W] fp32 -> [B,H,W,C] fp32 (entry of net._add_on(features) when called on its own). */
+int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream);
+
+/* im2col rows of a kxk convolution (pad, stride) over a channels-last bf16 map, K padded to Kpad with zeros:
+ * out[(b,ho,wo), (kh*k+kw)*C + c] -- feeds cpn_gemm_bf16 for features/resnet_features.py convs. */
+int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, int k, int stride,
+                    int pad, int Kpad, void* stream);
+/* Same gather from the fp32 NCHW network input (ResNet conv1 7x7 s2, features/resnet_features.py:139). */
+int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, int B, int C, int H, int W, int k, int stride,
+                        int pad, int Kpad, void* stream);
+/* MaxPool2d(3, stride 2, pad 1) on channels-last bf16 (features/resnet_features.py:142). */
+int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
+/* Strided row subsample of a channels-last bf16 map (1x1 stride-2 downsample conv input, resnet_features.py:178). */
+int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CPN_B200_H */

@@ -1,0 +1,207 @@
+"""Per-kernel numerics on the GPU: every C-ABI kernel against a plain PyTorch fp32 computation of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from count_pipnet_b200 import _lib, ops
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf16_split(t):
+    hi = t.to(torch.bfloat16)
+    lo = (t - hi.float()).to(torch.bfloat16)
+    return hi, lo
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 96, 64), (1000, 384, 96), (4096, 768, 192), (5000, 1536, 384),
+                                   (777, 192, 768), (3000, 3072, 768), (2048, 64, 152), (300, 32, 64)])
+def test_gemm_plain(cuda_device, M, N, K):
+    g = torch.Generator(device="cpu").manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    out = torch.empty(M, N, device=cuda_device)
+    ops.gemm_bf16(a, w, M, N, K, bias=bias, out_f32=out)
+    ref = a.float() @ w.float().t() + bias
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert err < 2e-3 * max(1.0, ref.abs().max().item()), err
+
+
+def test_gemm_gelu_bf16_out(cuda_device):
+    M, N, K = 3000, 768, 192
+    g = torch.Generator().manual_seed(1)
+    a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    out = torch.empty(M, N, device=cuda_device, dtype=torch.bfloat16)
+    ops.gemm_bf16(a, w, M, N, K, bias=bias, out_bf16=out, act=_lib.ACT_GELU)
+    ref = F.gelu(a.float() @ w.float().t() + bias)
+    torch.cuda.synchronize()
+    assert (out.float() - ref).abs().max().item() < 0.03
+
+
+def test_gemm_scale_residual_inplace(cuda_device):
+    M, N, K = 2500, 192, 768
+    g = torch.Generator().manual_seed(2)
+    a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    ls = torch.rand(N, generator=g).to(cuda_device)
+    res = torch.randn(M, N, generator=g).to(cuda_device)
+    ref = res + ls * (a.float() @ w.float().t() + bias)
+    ops.gemm_bf16(a, w, M, N, K, bias=bias, scale=ls, res_f32=res, out_f32=res)
+    torch.cuda.synchronize()
+    assert (res - ref).abs().max().item() < 5e-3
+
+
+def test_gemm_relu_bf16_residual(cuda_device):
+    M, N, K = 1568, 256, 64
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    res = torch.randn(M, N, generator=g).to(cuda_device).to(torch.bfloat16)
+    out = torch.empty(M, N, device=cuda_device, dtype=torch.bfloat16)
+    out32 = torch.empty(M, N, device=cuda_device)
+    ops.gemm_bf16(a, w, M, N, K, bias=bias, res_bf16=res, out_bf16=out, out_f32=out32, act=_lib.ACT_RELU,
+                  relu_after_res=True)
+    ref = torch.relu(a.float() @ w.float().t() + bias + res.float())
+    torch.cuda.synchronize()
+    assert (out32 - ref).abs().max().item() < 5e-3
+    assert (out.float() - ref).abs().max().item() < 0.05
+
+
+def test_gemm_split_fp32_mode(cuda_device):
+    """bf16x3 (hi/lo) GEMM must be ~fp32 accurate."""
+    M, N, K = 2000, 384, 1536
+    g = torch.Generator().manual_seed(4)
+    a = torch.randn(M, K, generator=g).to(cuda_device)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device)
+    a_hi, a_lo = _bf16_split(a)
+    w_hi, w_lo = _bf16_split(w)
+    out = torch.empty(M, N, device=cuda_device)
+    ops.gemm_bf16(a_hi, w_hi, M, N, K, a_lo=a_lo, bw_lo=w_lo, out_f32=out)
+    ref = (a.double() @ w.double().t()).float()
+    torch.cuda.synchronize()
+    rel = (out - ref).abs().max().item() / ref.abs().max().item()
+    assert rel < 5e-5, rel
+
+
+def test_stem_ln(cuda_device):
+    g = torch.Generator().manual_seed(5)
+    B, H, W = 3, 64, 96
+    x = torch.randn(B, 3, H, W, generator=g).to(cuda_device)
+    w = (torch.randn(96, 3, 4, 4, generator=g) * 0.2).to(cuda_device)
+    b = torch.randn(96, generator=g).to(cuda_device)
+    lw = torch.rand(96, generator=g).to(cuda_device) + 0.5
+    lb = torch.randn(96, generator=g).to(cuda_device)
+    out = torch.empty(B, H // 4, W // 4, 96, device=cuda_device)
+    ops.stem_ln(x, w.reshape(96, 48).contiguous(), b, lw, lb, out)
+    torch.backends.cudnn.allow_tf32 = False
+    y = F.conv2d(x, w, b, stride=4).permute(0, 2, 3, 1)
+    ref = F.layer_norm(y, (96,), lw, lb, 1e-6)
+    torch.cuda.synchronize()
+    assert (out - ref).abs().max().item() < 2e-4
+
+
+@pytest.mark.parametrize("B,H,W,C", [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192)])
+def test_dwconv7_ln(cuda_device, B, H, W, C):
+    g = torch.Generator().manual_seed(C + H)
+    x = torch.randn(B, H, W, C, generator=g).to(cuda_device)
+    w = (torch.randn(C, 1, 7, 7, generator=g) * 0.2).to(cuda_device)
+    b = torch.randn(C, generator=g).to(cuda_device)
+    lw = torch.rand(C, generator=g).to(cuda_device) + 0.5
+    lb = torch.randn(C, generator=g).to(cuda_device)
+    out = torch.empty(B * H * W, C, device=cuda_device, dtype=torch.bfloat16)
+    lo = torch.empty_like(out)
+    w49 = w.reshape(C, 49).t().contiguous()
+    ops.dwconv7_ln(x, w49, b, lw, lb, out, lo)
+    torch.backends.cudnn.allow_tf32 = False
+    y = F.conv2d(x.permute(0, 3, 1, 2), w, b, padding=3, groups=C).permute(0, 2, 3, 1)
+    ref = F.layer_norm(y, (C,), lw, lb, 1e-6).reshape(B * H * W, C)
+    torch.cuda.synchronize()
+    assert (out.float() - ref).abs().max().item() < 0.03
+    assert ((out.float() + lo.float()) - ref).abs().max().item() < 5e-4
+
+
+@pytest.mark.parametrize("stride,H,W,C", [(2, 16, 16, 96), (1, 14, 14, 192), (1, 9, 11, 384)])
+def test_ln_im2col2(cuda_device, stride, H, W, C):
+    g = torch.Generator().manual_seed(C)
+    B = 2
+    x = torch.randn(B, H, W, C, generator=g).to(cuda_device)
+    lw = torch.rand(C, generator=g).to(cuda_device) + 0.5
+    lb = torch.randn(C, generator=g).to(cuda_device)
+    Ho, Wo = (H - 2) // stride + 1, (W - 2) // stride + 1
+    out = torch.zeros(B * Ho * Wo, 4 * C, device=cuda_device, dtype=torch.bfloat16)
+    ops.ln_im2col2(x, lw, lb, out, stride=stride)
+    y = F.layer_norm(x, (C,), lw, lb, 1e-6)
+    cols = []
+    for kh in range(2):
+        for kw in range(2):
+            cols.append(y[:, kh:kh + stride * (Ho - 1) + 1:stride, kw:kw + stride * (Wo - 1) + 1:stride, :])
+    ref = torch.cat(cols, dim=-1).reshape(B * Ho * Wo, 4 * C)
+    torch.cuda.synchronize()
+    assert (out.float() - ref).abs().max().item() < 0.03
+
+
+@pytest.mark.parametrize("mode", [_lib.POOL_MAX, _lib.POOL_SUM])
+@pytest.mark.parametrize("P", [16, 768])
+def test_softmax_pool_and_map(cuda_device, mode, P):
+    g = torch.Generator().manual_seed(P)
+    B, HW, chunks = 3, 100, 4
+    z = (torch.randn(B, HW, P, generator=g) * 3).to(cuda_device)
+    partial = torch.empty(B, chunks, P, device=cuda_device)
+    pmap = torch.empty(B, P, HW, device=cuda_device)
+    ops.softmax_pool(z, partial, B, HW, P, chunks, mode=mode, map_out=pmap)
+    sm = torch.softmax(z, dim=2)
+    torch.cuda.synchronize()
+    assert (pmap - sm.permute(0, 2, 1)).abs().max().item() < 1e-6
+    if mode == _lib.POOL_MAX:
+        assert (partial.amax(1) - sm.amax(1)).abs().max().item() < 1e-6
+    else:
+        assert (partial.sum(1) - sm.sum(1)).abs().max().item() < 1e-4
+
+
+def test_softmax_pool_gumbel_hard(cuda_device):
+    g = torch.Generator().manual_seed(9)
+    B, HW, P, chunks = 2, 64, 16, 2
+    z = torch.randn(B, HW, P, generator=g).to(cuda_device)
+    noise = -torch.empty(B, P, HW).exponential_(generator=g).log()
+    noise = noise.to(cuda_device)
+    partial = torch.empty(B, chunks, P, device=cuda_device)
+    pmap = torch.empty(B, P, HW, device=cuda_device)
+    ops.softmax_pool(z, partial, B, HW, P, chunks, gumbel=noise, tau=0.7, hard=True, mode=_lib.POOL_SUM, map_out=pmap)
+    logits = (z.permute(0, 2, 1) + noise) / 0.7
+    y_soft = logits.softmax(1)
+    idx = y_soft.max(1, keepdim=True)[1]
+    y_hard = torch.zeros_like(y_soft).scatter_(1, idx, 1.0)
+    ref = y_hard - y_soft + y_soft
+    torch.cuda.synchronize()
+    assert (pmap - ref).abs().max().item() < 1e-6
+    assert (partial.sum(1) - ref.sum(2)).abs().max().item() < 1e-4
+
+
+def test_addon_conv(cuda_device):
+    g = torch.Generator().manual_seed(10)
+    T, C, P = 1000, 192, 16
+    f = torch.randn(T, C, generator=g).to(cuda_device)
+    w = torch.randn(P, C, generator=g).to(cuda_device) * 0.1
+    b = torch.randn(P, generator=g).to(cuda_device)
+    z = torch.empty(T, P, device=cuda_device)
+    ops.addon_conv1x1(f, w, b, z, T, C, P)
+    torch.cuda.synchronize()
+    assert (z - (f @ w.t() + b)).abs().max().item() < 1e-4
+
+
+def test_transposes(cuda_device):
+    x = torch.randn(2, 50, 70, device=cuda_device)
+    out = torch.empty(2, 70, 50, device=cuda_device)
+    ops.nhwc_to_nchw(x, out, 2, 50, 70)
+    torch.cuda.synchronize()
+    assert torch.equal(out, x.permute(0, 2, 1).contiguous())
+    back = torch.empty_like(x)
+    ops.nchw_to_nhwc(out, back, 2, 50, 70)
+    torch.cuda.synchronize()
+    assert torch.equal(back, x)
