@@ -30,8 +30,8 @@ SIGNATURES = {
     "cpn_nhwc_to_nchw": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_nchw_to_nhwc": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_im2col_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
-    "cpn_im2col_nchw_f32": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
-    "cpn_maxpool3s2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "cpn_im2col_nchw_f32": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "cpn_maxpool3s2": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_subsample2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
 }
 

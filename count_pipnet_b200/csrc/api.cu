@@ -413,26 +413,27 @@ int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int 
     });
 }
 
-int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, int B, int C, int H, int W, int k, int stride,
-                        int pad, int Kpad, void* stream) {
+int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, void* out_lo, int B, int C, int H, int W, int k,
+                        int stride, int pad, int Kpad, void* stream) {
     if (Kpad < k * k * C) return fail("cpn_im2col_nchw_f32: Kpad too small");
     const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
     const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * Kpad);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        cpn::im2col_nchw_f32_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(out), B, C, H, W, k, stride,
+        cpn::im2col_nchw_f32_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(out),
+                                                          static_cast<__nv_bfloat16*>(out_lo), B, C, H, W, k, stride,
                                                           pad, Ho, Wo, Kpad);
         CPN_CUDA(cudaGetLastError());
         return 0;
     });
 }
 
-int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream) {
-    if (C % 8 != 0) return fail("cpn_maxpool3s2_bf16: C must be a multiple of 8");
+int cpn_maxpool3s2(cpn_plan* plan, const float* x, float* out_f32, void* out_hi, void* out_lo, int B, int H, int W,
+                   int C, void* stream) {
     const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (C / 8));
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * C);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        cpn::maxpool3s2_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H,
-                                                          W, C, Ho, Wo);
+        cpn::maxpool3s2_kernel<<<grid, 256, 0, st>>>(x, out_f32, static_cast<__nv_bfloat16*>(out_hi),
+                                                     static_cast<__nv_bfloat16*>(out_lo), B, H, W, C, Ho, Wo);
         CPN_CUDA(cudaGetLastError());
         return 0;
     });

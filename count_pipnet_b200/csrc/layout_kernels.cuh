@@ -53,8 +53,8 @@ im2col_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, 
 
 // im2col straight from the fp32 NCHW network input; column = c*k*k + kh*k + kw (the torch weight flattening).
 __global__ void __launch_bounds__(256)
-im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int C, int H, int W, int k,
-                       int stride, int pad, int Ho, int Wo, int Kpad) {
+im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo,
+                       int B, int C, int H, int W, int k, int stride, int pad, int Ho, int Wo, int Kpad) {
     const long long total = static_cast<long long>(B) * Ho * Wo * Kpad;
     const int kk = k * k;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -72,46 +72,40 @@ im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ 
             if (hi >= 0 && hi < H && wi >= 0 && wi < W)
                 v = __ldg(x + ((static_cast<size_t>(b) * C + c) * H + hi) * W + wi);
         }
-        out[i] = __float2bfloat16_rn(v);
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        out[i] = h;
+        if (out_lo != nullptr) out_lo[i] = __float2bfloat16_rn(v - __bfloat162float(h));
     }
 }
 
-__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
-    __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a);
-    __nv_bfloat162 y = *reinterpret_cast<__nv_bfloat162*>(&b);
-    __nv_bfloat162 m = __hmax2(x, y);
-    return *reinterpret_cast<uint32_t*>(&m);
-}
-
-// MaxPool2d(kernel 3, stride 2, pad 1), channels-last bf16, 8 channels per thread.
+// MaxPool2d(kernel 3, stride 2, pad 1) on a channels-last fp32 map; writes fp32 and/or the bf16 hi (+lo) planes.
 __global__ void __launch_bounds__(256)
-maxpool3s2_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
-    const int c8 = C >> 3;
-    const long long total = static_cast<long long>(B) * Ho * Wo * c8;
+maxpool3s2_kernel(const float* __restrict__ x, float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_hi,
+                  __nv_bfloat16* __restrict__ out_lo, int B, int H, int W, int C, int Ho, int Wo) {
+    const long long total = static_cast<long long>(B) * Ho * Wo * C;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
-        const int cc = static_cast<int>(i % c8);
-        const long long row = i / c8;
+        const int c = static_cast<int>(i % C);
+        const long long row = i / C;
         const int wo = static_cast<int>(row % Wo);
         const int ho = static_cast<int>((row / Wo) % Ho);
         const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
-        bool first = true;
-        uint4 m = make_uint4(0u, 0u, 0u, 0u);
+        float m = -INFINITY;
         for (int kh = 0; kh < 3; ++kh) {
             const int hi = ho * 2 - 1 + kh;
             if (hi < 0 || hi >= H) continue;
             for (int kw = 0; kw < 3; ++kw) {
                 const int wi = wo * 2 - 1 + kw;
                 if (wi < 0 || wi >= W) continue;
-                const uint4 v = __ldg(x + ((static_cast<size_t>(b) * H + hi) * W + wi) * c8 + cc);
-                if (first) { m = v; first = false; }
-                else {
-                    m.x = bf16x2_max(m.x, v.x); m.y = bf16x2_max(m.y, v.y);
-                    m.z = bf16x2_max(m.z, v.z); m.w = bf16x2_max(m.w, v.w);
-                }
+                m = fmaxf(m, __ldg(x + ((static_cast<size_t>(b) * H + hi) * W + wi) * C + c));
             }
         }
-        out[i] = m;
+        if (out_f32 != nullptr) out_f32[i] = m;
+        if (out_hi != nullptr) {
+            const __nv_bfloat16 h = __float2bfloat16_rn(m);
+            out_hi[i] = h;
+            if (out_lo != nullptr) out_lo[i] = __float2bfloat16_rn(m - __bfloat162float(h));
+        }
     }
 }
 

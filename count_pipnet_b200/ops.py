@@ -126,14 +126,15 @@ def im2col_bf16(x, out, B, H, W, Cc, k, stride, pad, Kpad, plan=None):
     _lib.call("cpn_im2col_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, k, stride, pad, Kpad, _stream())
 
 
-def im2col_nchw_f32(x, out, B, Cc, H, W, k, stride, pad, Kpad, plan=None):
-    _need_cuda(x, out)
-    _lib.call("cpn_im2col_nchw_f32", _ph(plan), ptr(x), ptr(out), B, Cc, H, W, k, stride, pad, Kpad, _stream())
+def im2col_nchw_f32(x, out, B, Cc, H, W, k, stride, pad, Kpad, out_lo=None, plan=None):
+    _need_cuda(x, out, out_lo)
+    _lib.call("cpn_im2col_nchw_f32", _ph(plan), ptr(x), ptr(out), ptr(out_lo), B, Cc, H, W, k, stride, pad, Kpad,
+              _stream())
 
 
-def maxpool3s2_bf16(x, out, B, H, W, Cc, plan=None):
-    _need_cuda(x, out)
-    _lib.call("cpn_maxpool3s2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())
+def maxpool3s2(x, B, H, W, Cc, out_f32=None, out_hi=None, out_lo=None, plan=None):
+    _need_cuda(x, out_f32, out_hi, out_lo)
+    _lib.call("cpn_maxpool3s2", _ph(plan), ptr(x), ptr(out_f32), ptr(out_hi), ptr(out_lo), B, H, W, Cc, _stream())
 
 
 def subsample2_bf16(x, out, B, H, W, Cc, plan=None):

@@ -114,10 +114,12 @@ int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, 
 int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, int k, int stride,
                     int pad, int Kpad, void* stream);
 /* Same gather from the fp32 NCHW network input (ResNet conv1 7x7 s2, features/resnet_features.py:139). */
-int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, int B, int C, int H, int W, int k, int stride,
-                        int pad, int Kpad, void* stream);
-/* MaxPool2d(3, stride 2, pad 1) on channels-last bf16 (features/resnet_features.py:142). */
-int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
+int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, void* out_lo, int B, int C, int H, int W, int k,
+                        int stride, int pad, int Kpad, void* stream);
+/* MaxPool2d(3, stride 2, pad 1) on a channels-last fp32 map (features/resnet_features.py:142); any of the outputs
+ * (fp32, bf16 hi, bf16 lo) may be NULL. */
+int cpn_maxpool3s2(cpn_plan* plan, const float* x, float* out_f32, void* out_hi, void* out_lo, int B, int H, int W,
+                   int C, void* stream);
 /* Strided row subsample of a channels-last bf16 map (1x1 stride-2 downsample conv input, resnet_features.py:178). */
 int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
 

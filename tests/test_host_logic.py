@@ -1,0 +1,119 @@
+"""CPU: the host side of the drop-in - module tree / state-dict names, factory behaviour, composed (autograd) path
+against the oracle, dispatch rules, and that the C-ABI library loads and exports everything include/cpn_b200.h declares."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+import oracle
+from count_pipnet_b200 import _lib, engine, synth
+from count_pipnet_b200.features import convnext_features as cf
+from count_pipnet_b200.pipnet import count_pipnet as my_count
+from count_pipnet_b200.pipnet import pipnet as my_pipnet
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported():
+    header = open(os.path.join(ROOT, "include", "cpn_b200.h")).read()
+    declared = set(re.findall(r"\b(cpn_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    missing = [s for s in sorted(declared) if not hasattr(lib, s)]
+    assert not missing, missing
+    assert set(_lib.SIGNATURES) | {"cpn_last_error"} == declared
+
+
+def test_library_loads_and_reports_errors_without_gpu():
+    lib = _lib.load()
+    assert lib.cpn_version() >= 100
+    h = ctypes.c_void_p()
+    assert lib.cpn_plan_create(ctypes.byref(h)) == 0 and lib.cpn_plan_num_ops(h) == 0
+    assert lib.cpn_plan_destroy(h) == 0
+    # argument validation happens before any CUDA call
+    rc = lib.cpn_gemm_bf16(None, None, None, None, None, 128, 100, 64, None, None, None, None, None, None, None, 0, 0,
+                           None)
+    assert rc != 0 and b"multiple of 32" in lib.cpn_last_error()
+
+
+def test_state_dict_names_convnext():
+    model, p = my_pipnet.get_pipnet(200, synth.make_args())
+    keys = list(model.state_dict().keys())
+    assert p == 768
+    for k in ["_net.features.0.0.weight", "_net.features.0.1.bias", "_net.features.1.0.layer_scale",
+              "_net.features.1.2.block.0.weight", "_net.features.5.8.block.5.bias", "_net.features.6.1.weight",
+              "_net.features.7.2.block.3.weight", "_classification.weight",
+              "_classification.normalization_multiplier", "_multiplier"]:
+        assert k in keys, k
+    assert model.state_dict()["_net.features.7.2.block.3.weight"].shape == (3072, 768)
+    # stride surgery of the "26" variant: 96->192 keeps stride 2, the two later downsample convs run at stride 1
+    strides = [m.stride for m in model._net.modules() if isinstance(m, torch.nn.Conv2d) and m.kernel_size == (2, 2)]
+    assert strides == [(2, 2), (1, 1), (1, 1)]
+    m13 = cf.convnext_tiny_13_features()
+    strides = [m.stride for m in m13.modules() if isinstance(m, torch.nn.Conv2d) and m.kernel_size == (2, 2)]
+    assert strides == [(2, 2), (2, 2), (1, 1)]
+
+
+@pytest.mark.parametrize("num_stages,channels,grid192", [(1, 96, 48), (2, 192, 24), (3, 192, 24), (4, 384, 23),
+                                                          (5, 384, 23), (6, 768, 22), (7, 768, 22)])
+def test_mid_layer_shapes(num_stages, channels, grid192):
+    """Per-stage shape table of the reference (tests/test-convnext-backbone.py)."""
+    shape = cf.get_feature_dimensions(use_mid_layers=True, num_stages=num_stages, input_size=192)
+    assert tuple(shape) == (1, channels, grid192, grid192)
+
+
+def test_count_network_factory_and_errors():
+    args = synth.make_args(num_features=16, use_mid_layers=True, num_stages=3, intermediate_layer="bilinear",
+                           activation="gumbel_softmax")
+    model, p = my_count.get_count_network(9, args, max_count=3, use_ste=True)
+    assert p == 16 and model._classification.weight.shape == (9, 48) and hasattr(model, "_max_count")
+    assert "_intermediate.embed.weight" in model.state_dict()
+    with pytest.raises(ValueError):
+        my_count.get_count_network(9, synth.make_args(net="resnet50"))
+    with pytest.raises(ValueError):
+        my_count.get_count_network(9, synth.make_args(intermediate_layer="nope"))
+    with pytest.raises(Exception):
+        my_pipnet.get_pipnet(9, synth.make_args(net="vgg"))
+    model.update_temperature(0.3)
+    assert model._add_on[-1].tau == 0.3
+    onehot, _ = my_count.get_count_network(9, synth.make_args(num_features=16, use_mid_layers=True, num_stages=3))
+    assert onehot.get_prototype_importance_per_class(0).shape == (9,)
+
+
+@pytest.mark.parametrize("name", ["count_linear_softmax", "count_identity_softmax_noste",
+                                  "count_linear_full_softmax_train_outputs", "pipnet_convnext13_addon32_bias",
+                                  "pipnet_resnet18_64"])
+def test_composed_path_equals_oracle(name):
+    """With autograd enabled the modules run composed PyTorch ops; that path must equal the reference arithmetic."""
+    case = cases.CASES[name]
+    model = cases.build(case, my_pipnet, my_count)
+    x = cases.inputs(case)
+    sd = {k: v.detach() for k, v in model.state_dict().items()}
+    with torch.enable_grad():
+        proto, pooled, out = model(x, inference=case["inference"])
+    assert out.requires_grad
+    o_proto, o_pooled, o_out = oracle.forward(sd, cases.oracle_cfg(case), x, inference=case["inference"])
+    assert torch.allclose(proto, o_proto, atol=1e-6) and torch.allclose(pooled, o_pooled, atol=1e-5)
+    assert torch.allclose(out, o_out, rtol=1e-5, atol=1e-5)
+
+
+def test_inference_on_cpu_raises_no_fallback():
+    model, _ = my_pipnet.get_pipnet(5, synth.make_args(use_mid_layers=True, num_stages=1))
+    model.eval()
+    with torch.no_grad(), pytest.raises(_lib.CpnError):
+        model(torch.zeros(1, 3, 32, 32), inference=True)
+    model.train()
+    assert engine.use_fused(model, torch.zeros(1, 3, 32, 32)) is False
+
+
+def test_synth_weights_are_deterministic():
+    model, _ = my_pipnet.get_pipnet(7, synth.make_args(use_mid_layers=True, num_stages=2))
+    a = synth.synth_state_dict(model.state_dict(), seed=3)
+    b = synth.synth_state_dict(model.state_dict(), seed=3)
+    assert all(torch.equal(a[k], b[k]) for k in a)
+    w = a["_classification.weight"]
+    assert ((w > 0).sum(1) == 8).all() and float(a["_multiplier"]) == 2.0
