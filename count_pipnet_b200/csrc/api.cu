@@ -40,6 +40,19 @@ int fail(const char* fmt, ...) {
 
 using Launch = std::function<int(cudaStream_t)>;
 
+// Algorithmic work of the op being submitted (for cpn_plan_run_timed's per-op report); set by each entry point.
+struct OpInfo {
+    const char* name = "op";
+    double flops = 0.0;
+    double bytes = 0.0;
+};
+thread_local OpInfo g_info;
+void set_info(const char* name, double flops, double bytes) {
+    g_info.name = name;
+    g_info.flops = flops;
+    g_info.bytes = bytes;
+}
+
 int submit(cpn_plan* plan, void* stream, Launch fn);
 
 // ------------------------------------------------------------------------------------------------ TMA descriptors
@@ -157,12 +170,14 @@ int pick_bn(int M, int N, bool split) {
 // ------------------------------------------------------------------------------------------------ plan
 struct cpn_plan {
     std::vector<Launch> ops;
+    std::vector<OpInfo> info;
 };
 
 namespace {
 int submit(cpn_plan* plan, void* stream, Launch fn) {
     if (plan != nullptr) {
         plan->ops.push_back(std::move(fn));
+        plan->info.push_back(g_info);
         return 0;
     }
     return fn(static_cast<cudaStream_t>(stream));
@@ -201,6 +216,35 @@ int cpn_plan_run(cpn_plan* plan, void* stream) {
     return 0;
 }
 
+int cpn_plan_run_timed(cpn_plan* plan, void* stream, float* ms_out, int n) {
+    if (plan == nullptr || ms_out == nullptr) return fail("cpn_plan_run_timed: null argument");
+    const int nops = static_cast<int>(plan->ops.size());
+    if (n < nops) return fail("cpn_plan_run_timed: output holds %d entries, plan has %d ops", n, nops);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    std::vector<cudaEvent_t> ev(nops + 1);
+    for (auto& e : ev) CPN_CUDA(cudaEventCreate(&e));
+    CPN_CUDA(cudaEventRecord(ev[0], st));
+    int rc = 0;
+    for (int i = 0; i < nops && rc == 0; ++i) {
+        rc = plan->ops[i](st);
+        if (rc == 0) CPN_CUDA(cudaEventRecord(ev[i + 1], st));
+    }
+    if (rc == 0) {
+        CPN_CUDA(cudaEventSynchronize(ev[nops]));
+        for (int i = 0; i < nops; ++i) CPN_CUDA(cudaEventElapsedTime(&ms_out[i], ev[i], ev[i + 1]));
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    return rc;
+}
+
+int cpn_plan_op_info(const cpn_plan* plan, int i, const char** name, double* flops, double* bytes) {
+    if (plan == nullptr || i < 0 || i >= static_cast<int>(plan->info.size())) return fail("cpn_plan_op_info: bad index");
+    if (name != nullptr) *name = plan->info[i].name;
+    if (flops != nullptr) *flops = plan->info[i].flops;
+    if (bytes != nullptr) *bytes = plan->info[i].bytes;
+    return 0;
+}
+
 int cpn_plan_num_ops(const cpn_plan* plan) { return plan == nullptr ? -1 : static_cast<int>(plan->ops.size()); }
 
 int cpn_plan_destroy(cpn_plan* plan) {
@@ -218,6 +262,7 @@ int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bia
     const long long cap = static_cast<long long>(num_sms()) * 2;  // weights live in registers: keep CTAs persistent
     if (blocks > cap) blocks = cap;
     const int grid = static_cast<int>(blocks);
+    set_info("stem_ln", 2.0 * 48 * 96 * B * Ho * Wo, 4.0 * B * (3.0 * H * W + 96.0 * Ho * Wo));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::stem_ln_kernel<<<grid, cpn::STEM_WARPS * 32, 0, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());
@@ -239,6 +284,7 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
     const dim3 grid(strips, (H + rows - 1) / rows, B);
     auto* hi = static_cast<__nv_bfloat16*>(out_hi);
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
+    set_info("dwconv7_ln", 2.0 * 49 * B * H * W * C, 1.0 * B * H * W * C * (4 + 2 + (out_lo != nullptr ? 2 : 0)));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (tw == 2)
             cpn::dwconv7_ln_kernel<2><<<grid, threads, 0, st>>>(x, w49, bias, ln_w, ln_b, hi, lo, H, W, C, rows, eps);
@@ -259,6 +305,7 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
     const int grid = static_cast<int>((ntok + 7) / 8);
     auto* hi = static_cast<__nv_bfloat16*>(out_hi);
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
+    set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::ln_im2col2_kernel<<<grid, 256, 0, st>>>(x, ln_w, ln_b, hi, lo, B, H, W, C, stride, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());
@@ -301,6 +348,16 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
     g.p.relu_after_res = relu_after_res;
     const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
     g.grid = tiles < num_sms() ? tiles : num_sms();
+    {
+        double bytes = 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) * (split ? 2 : 1);
+        const double mn = static_cast<double>(M) * N;
+        if (res_f32 != nullptr) bytes += 4.0 * mn;
+        if (res_bf16 != nullptr) bytes += 2.0 * mn;
+        if (out_f32 != nullptr) bytes += 4.0 * mn;
+        if (out_bf16 != nullptr) bytes += 2.0 * mn;
+        if (out_bf16_lo != nullptr) bytes += 2.0 * mn;
+        set_info(split ? "gemm_bf16x3" : "gemm_bf16", 2.0 * mn * K * (split ? 3 : 1), bytes);
+    }
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         return split ? launch_gemm_bn<true>(g, bn, act, st) : launch_gemm_bn<false>(g, bn, act, st);
     });
@@ -314,6 +371,7 @@ int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const f
     long long blocks = (T + 7) / 8;
     if (blocks > 4LL * num_sms()) blocks = 4LL * num_sms();
     const int grid = static_cast<int>(blocks);
+    set_info("addon_conv1x1", 2.0 * T * C * P, 4.0 * T * (C + P));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::addon_conv1x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -330,6 +388,7 @@ int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float 
     const size_t smem = 8 * static_cast<size_t>(P) * sizeof(float);
     if (smem > 200 * 1024) return fail("cpn_softmax_pool: P=%d too large", P);
     const dim3 grid(chunks, B);
+    set_info("softmax_pool", 4.0 * B * HW * P, 4.0 * B * HW * P * (1 + (gumbel != nullptr) + (map != nullptr)));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -365,6 +424,7 @@ int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, in
     }
     const size_t smem = (static_cast<size_t>(P) + 2 * static_cast<size_t>(D)) * sizeof(float);
     if (smem > 200 * 1024) return fail("cpn_head_tail: P=%d D=%d too large", P, D);
+    set_info("head_tail", 2.0 * B * D * K, 4.0 * B * (1.0 * chunks * P + 1.0 * D * K));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -378,6 +438,7 @@ int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, in
 // ------------------------------------------------------------------------------------------------ layout / ResNet helpers
 int cpn_nhwc_to_nchw(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream) {
     const dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
+    set_info("nhwc_to_nchw", 0.0, 8.0 * B * HW * C);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::transpose_last2_kernel<<<grid, 256, 0, st>>>(x, out, HW, C);
         CPN_CUDA(cudaGetLastError());
@@ -387,6 +448,7 @@ int cpn_nhwc_to_nchw(cpn_plan* plan, const float* x, float* out, int B, int HW, 
 
 int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream) {
     const dim3 grid((C + 31) / 32, (HW + 31) / 32, B);
+    set_info("nchw_to_nhwc", 0.0, 8.0 * B * HW * C);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::transpose_last2_kernel<<<grid, 256, 0, st>>>(x, out, C, HW);
         CPN_CUDA(cudaGetLastError());
@@ -405,6 +467,7 @@ int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int 
     if (C % 8 != 0 || Kpad % 8 != 0 || Kpad < k * k * C) return fail("cpn_im2col_bf16: bad C=%d Kpad=%d", C, Kpad);
     const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
     const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (Kpad / 8));
+    set_info("im2col_bf16", 0.0, 4.0 * B * Ho * Wo * Kpad);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::im2col_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H, W, C,
                                                       k, stride, pad, Ho, Wo, Kpad);
@@ -418,6 +481,7 @@ int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, void* out_lo,
     if (Kpad < k * k * C) return fail("cpn_im2col_nchw_f32: Kpad too small");
     const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
     const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * Kpad);
+    set_info("im2col_nchw_f32", 0.0, 4.0 * B * C * H * W + 2.0 * B * Ho * Wo * Kpad * (out_lo != nullptr ? 2 : 1));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::im2col_nchw_f32_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(out),
                                                           static_cast<__nv_bfloat16*>(out_lo), B, C, H, W, k, stride,
@@ -431,6 +495,7 @@ int cpn_maxpool3s2(cpn_plan* plan, const float* x, float* out_f32, void* out_hi,
                    int C, void* stream) {
     const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
     const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * C);
+    set_info("maxpool3s2", 0.0, 4.0 * B * H * W * C + 1.0 * B * Ho * Wo * C * ((out_f32 != nullptr) * 4 + (out_hi != nullptr) * 2 + (out_lo != nullptr) * 2));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::maxpool3s2_kernel<<<grid, 256, 0, st>>>(x, out_f32, static_cast<__nv_bfloat16*>(out_hi),
                                                      static_cast<__nv_bfloat16*>(out_lo), B, H, W, C, Ho, Wo);
@@ -443,6 +508,7 @@ int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, 
     if (C % 8 != 0) return fail("cpn_subsample2_bf16: C must be a multiple of 8");
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
     const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (C / 8));
+    set_info("subsample2_bf16", 0.0, 4.0 * B * Ho * Wo * C);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::subsample2_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H,
                                                           W, C, Ho, Wo);

@@ -41,6 +41,19 @@ class Plan:
     def __len__(self) -> int:
         return _lib.load().cpn_plan_num_ops(self.handle)
 
+    def run_timed(self):
+        """Replay with an event after every op; returns [(name, ms, flops, bytes)] (synchronises)."""
+        lib = _lib.load()
+        n = len(self)
+        ms = (C.c_float * n)()
+        _lib.check(lib.cpn_plan_run_timed(self.handle, _stream(), ms, n))
+        out = []
+        for i in range(n):
+            name, fl, by = C.c_char_p(), C.c_double(), C.c_double()
+            _lib.check(lib.cpn_plan_op_info(self.handle, i, C.byref(name), C.byref(fl), C.byref(by)))
+            out.append((name.value.decode(), float(ms[i]), fl.value, by.value))
+        return out
+
     def __del__(self):
         try:
             if self.handle:

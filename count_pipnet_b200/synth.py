@@ -88,6 +88,13 @@ def synth_state_dict(template: Dict[str, torch.Tensor], seed: int = 0, gain: flo
             v = _normal(shape, gain / math.sqrt(fan_in), g)
         elif leaf == "weight":   # LayerNorm / BatchNorm scale
             v = _uniform(shape, 0.5, 1.5, g)
+            # ResNet: damp the BN that closes a residual branch (and the projection shortcut) so that the summed
+            # stream keeps |z|max ~ 10 at the softmax instead of growing block over block (measured: 53 -> 13)
+            stem = key[: -len("weight")]
+            closes_branch = key.endswith("bn3.weight") or \
+                (key.endswith("bn2.weight") and (stem[:-4] + "bn3.weight") not in template)
+            if "_net.layer" in key and (closes_branch or "downsample.1." in key):
+                v = v * 0.8
         elif leaf == "bias":
             v = _normal(shape, 0.1, g)
         else:

@@ -52,6 +52,10 @@ int cpn_check_device(void);
 int cpn_plan_create(cpn_plan** out);
 int cpn_plan_run(cpn_plan* plan, void* stream);
 int cpn_plan_num_ops(const cpn_plan* plan);
+/* Replay with a CUDA event between consecutive ops; ms_out[i] = device time of op i (synchronises at the end). */
+int cpn_plan_run_timed(cpn_plan* plan, void* stream, float* ms_out, int n);
+/* Kernel family name and algorithmic FLOPs / HBM bytes of op i (what the roofline fractions are computed from). */
+int cpn_plan_op_info(const cpn_plan* plan, int i, const char** name, double* flops, double* bytes);
 int cpn_plan_destroy(cpn_plan* plan);
 
 /* ---- ConvNeXt feature path --------------------------------------------------------------------------------- */

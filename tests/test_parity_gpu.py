@@ -54,9 +54,17 @@ def test_fused_forward_matches_reference_golden(cuda_device, name, precision):
     errs["map_max"] = rel(flat.amax(2).cpu().numpy(), g["map_max"])
     print(f"{name} [{precision}] " + " ".join(f"{k}={v:.2e}" for k, v in errs.items()))
     is_count_inf = case["model"] == "count_pipnet" and case["inference"]
-    if is_count_inf:
+    if is_count_inf and precision == "fp32":
         # counts are integers: exact or wrong
         assert np.array_equal(pooled, g["pooled"]), (pooled - g["pooled"]).nonzero()
+    elif is_count_inf:
+        # bf16 mode: a count is round(sum of patch probabilities); it may only differ from the reference where the
+        # reference's raw sum (golden map_sum) sits within the bf16-mode tolerance of a rounding boundary
+        raw = np.clip(g["map_sum"], 0, case["max_count"] + 0.49)
+        near_boundary = np.abs(raw - np.floor(raw) - 0.5) <= tol * np.maximum(1.0, raw)
+        bad = (pooled != g["pooled"]) & ~near_boundary
+        assert not bad.any(), np.argwhere(bad)
+        assert (pooled != g["pooled"]).mean() <= 0.02
     else:
         assert errs["pooled"] <= tol, errs
     assert errs["out"] <= tol, errs
