@@ -42,6 +42,13 @@ POOL_MAX, POOL_SUM = 0, 1
 ENC_NONE, ENC_ONEHOT, ENC_LINEAR, ENC_LINEAR_FULL, ENC_BILINEAR, ENC_IDENTITY = 0, 1, 2, 3, 4, 5
 
 
+# entry points that do not return an int status: name -> (argtypes, restype)
+OTHER_SIGNATURES = {
+    "cpn_last_error": ([], C.c_char_p),
+    "cpn_plan_op_detail": ([_vp, _i], C.c_char_p),
+}
+
+
 class CpnError(RuntimeError):
     pass
 
@@ -63,8 +70,10 @@ def load():
             fn = getattr(lib, name)
             fn.argtypes = args
             fn.restype = C.c_int
-        lib.cpn_last_error.argtypes = []
-        lib.cpn_last_error.restype = C.c_char_p
+        for name, (args, res) in OTHER_SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.argtypes = args
+            fn.restype = res
         _LIB = lib
     return _LIB
 

@@ -45,12 +45,22 @@ struct OpInfo {
     const char* name = "op";
     double flops = 0.0;
     double bytes = 0.0;
+    std::string detail;  // shape of this launch, for per-op reports
 };
 thread_local OpInfo g_info;
-void set_info(const char* name, double flops, double bytes) {
+void set_info(const char* name, double flops, double bytes, const char* fmt = nullptr, ...) {
     g_info.name = name;
     g_info.flops = flops;
     g_info.bytes = bytes;
+    g_info.detail.clear();
+    if (fmt != nullptr) {
+        char buf[160];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        g_info.detail = buf;
+    }
 }
 
 int submit(cpn_plan* plan, void* stream, Launch fn);
@@ -245,6 +255,11 @@ int cpn_plan_op_info(const cpn_plan* plan, int i, const char** name, double* flo
     return 0;
 }
 
+const char* cpn_plan_op_detail(const cpn_plan* plan, int i) {
+    if (plan == nullptr || i < 0 || i >= static_cast<int>(plan->info.size())) return "";
+    return plan->info[i].detail.c_str();
+}
+
 int cpn_plan_num_ops(const cpn_plan* plan) { return plan == nullptr ? -1 : static_cast<int>(plan->ops.size()); }
 
 int cpn_plan_destroy(cpn_plan* plan) {
@@ -262,7 +277,7 @@ int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bia
     const long long cap = static_cast<long long>(num_sms()) * 2;  // weights live in registers: keep CTAs persistent
     if (blocks > cap) blocks = cap;
     const int grid = static_cast<int>(blocks);
-    set_info("stem_ln", 2.0 * 48 * 96 * B * Ho * Wo, 4.0 * B * (3.0 * H * W + 96.0 * Ho * Wo));
+    set_info("stem_ln", 2.0 * 48 * 96 * B * Ho * Wo, 4.0 * B * (3.0 * H * W + 96.0 * Ho * Wo), "B=%d H=%d W=%d", B, H, W);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::stem_ln_kernel<<<grid, cpn::STEM_WARPS * 32, 0, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());
@@ -284,7 +299,8 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
     const dim3 grid(strips, (H + rows - 1) / rows, B);
     auto* hi = static_cast<__nv_bfloat16*>(out_hi);
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
-    set_info("dwconv7_ln", 2.0 * 49 * B * H * W * C, 1.0 * B * H * W * C * (4 + 2 + (out_lo != nullptr ? 2 : 0)));
+    set_info("dwconv7_ln", 2.0 * 49 * B * H * W * C, 1.0 * B * H * W * C * (4 + 2 + (out_lo != nullptr ? 2 : 0)),
+             "B=%d H=%d W=%d C=%d", B, H, W, C);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (tw == 2)
             cpn::dwconv7_ln_kernel<2><<<grid, threads, 0, st>>>(x, w49, bias, ln_w, ln_b, hi, lo, H, W, C, rows, eps);
@@ -305,7 +321,8 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
     const int grid = static_cast<int>((ntok + 7) / 8);
     auto* hi = static_cast<__nv_bfloat16*>(out_hi);
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
-    set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2));
+    set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2),
+             "B=%d H=%d W=%d C=%d s=%d", B, H, W, C, stride);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::ln_im2col2_kernel<<<grid, 256, 0, st>>>(x, ln_w, ln_b, hi, lo, B, H, W, C, stride, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());
@@ -356,7 +373,8 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
         if (out_f32 != nullptr) bytes += 4.0 * mn;
         if (out_bf16 != nullptr) bytes += 2.0 * mn;
         if (out_bf16_lo != nullptr) bytes += 2.0 * mn;
-        set_info(split ? "gemm_bf16x3" : "gemm_bf16", 2.0 * mn * K * (split ? 3 : 1), bytes);
+        set_info(split ? "gemm_bf16x3" : "gemm_bf16", 2.0 * mn * K * (split ? 3 : 1), bytes, "M=%d N=%d K=%d BN=%d act=%d res=%d",
+                 M, N, K, bn, act, res_f32 != nullptr || res_bf16 != nullptr);
     }
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         return split ? launch_gemm_bn<true>(g, bn, act, st) : launch_gemm_bn<false>(g, bn, act, st);

@@ -54,6 +54,11 @@ class Plan:
             out.append((name.value.decode(), float(ms[i]), fl.value, by.value))
         return out
 
+    def details(self):
+        """Shape string of every recorded op (same order as run_timed)."""
+        lib = _lib.load()
+        return [(lib.cpn_plan_op_detail(self.handle, i) or b"").decode() for i in range(len(self))]
+
     def __del__(self):
         try:
             if self.handle:

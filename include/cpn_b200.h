@@ -56,6 +56,8 @@ int cpn_plan_num_ops(const cpn_plan* plan);
 int cpn_plan_run_timed(cpn_plan* plan, void* stream, float* ms_out, int n);
 /* Kernel family name and algorithmic FLOPs / HBM bytes of op i (what the roofline fractions are computed from). */
 int cpn_plan_op_info(const cpn_plan* plan, int i, const char** name, double* flops, double* bytes);
+/* Shape string of op i ("M=.. N=.. K=.."), for per-launch reports; "" if none. */
+const char* cpn_plan_op_detail(const cpn_plan* plan, int i);
 int cpn_plan_destroy(cpn_plan* plan);
 
 /* ---- ConvNeXt feature path --------------------------------------------------------------------------------- */

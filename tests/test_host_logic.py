@@ -25,7 +25,7 @@ def test_header_symbols_exported():
     lib = ctypes.CDLL(_lib.LIB_PATH)
     missing = [s for s in sorted(declared) if not hasattr(lib, s)]
     assert not missing, missing
-    assert set(_lib.SIGNATURES) | {"cpn_last_error"} == declared
+    assert set(_lib.SIGNATURES) | set(_lib.OTHER_SIGNATURES) == declared
 
 
 def test_library_loads_and_reports_errors_without_gpu():

@@ -65,6 +65,15 @@ def test_fused_forward_matches_reference_golden(cuda_device, name, precision):
         bad = (pooled != g["pooled"]) & ~near_boundary
         assert not bad.any(), np.argwhere(bad)
         assert (pooled != g["pooled"]).mean() <= 0.02
+    elif case["model"] == "pipnet" and case["inference"]:
+        # pooled = where(max < 0.1, 0, max) (pipnet/pipnet.py:36) is discontinuous at 0.1: a score whose reference
+        # maximum (golden map_max) lies within the tolerance of the threshold may land on either side of it; there
+        # the un-thresholded value must still match. Everywhere else the thresholded values are compared.
+        scale = np.abs(g["pooled"]).max()
+        near = np.abs(g["map_max"] - 0.1) <= tol * scale
+        assert near.mean() <= 0.1
+        raw = np.where(pooled == 0.0, g["map_max"], pooled)  # what the kernel saw before the threshold, if it kept it
+        assert np.abs(np.where(near, raw - g["map_max"], pooled - g["pooled"])).max() <= tol * scale, errs
     else:
         assert errs["pooled"] <= tol, errs
     assert errs["out"] <= tol, errs
