@@ -7,6 +7,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <mutex>
@@ -14,6 +15,7 @@
 #include <vector>
 
 #include "convnext_kernels.cuh"
+#include "dwconv_tma.cuh"
 #include "gemm_tcgen05.cuh"
 #include "head_kernels.cuh"
 #include "layout_kernels.cuh"
@@ -98,6 +100,26 @@ int make_tmap(CUtensorMap* m, const void* ptr, long long rows, int K, int box_ro
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld K=%d box_rows=%d)",
                                        static_cast<int>(r), rows, K, box_rows);
+    return 0;
+}
+
+// fp32 channels-last map [B,H,W,C] as a 4-D tensor (C innermost), box = cb channels x ntok tokens of one row.
+int make_tmap_nhwc_f32(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int cb, int ntok) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA operand not 16-byte aligned");
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(B)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 4, static_cast<cuuint64_t>(W) * C * 4,
+                             static_cast<cuuint64_t>(H) * W * C * 4};
+    cuuint32_t box[4] = {static_cast<cuuint32_t>(cb), static_cast<cuuint32_t>(ntok), 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail("cuTensorMapEncodeTiled (4-D fp32) failed with CUresult %d (B=%d H=%d W=%d C=%d box=%dx%d)",
+                    static_cast<int>(r), B, H, W, C, cb, ntok);
     return 0;
 }
 
@@ -192,6 +214,86 @@ int submit(cpn_plan* plan, void* stream, Launch fn) {
     }
     return fn(static_cast<cudaStream_t>(stream));
 }
+}  // namespace
+
+namespace {
+// Launch geometry of the TMA depthwise kernel: threads per strip (channel pairs rounded up to whole warps), strips
+// per CTA G, tokens per strip TW and row chunks, chosen by a wave-count x rows x TW cost model.
+struct Dw2Geom {
+    bool ok = false;
+    int NT = 192, G = 1, gthreads = 0, TW = 4, chunks = 1, CB = 0, nbox = 1, nst = 4;
+    int box_bytes = 0, stage_bytes = 0;
+    size_t smem = 0;
+};
+
+Dw2Geom dw2_geometry(int B, int H, int W, int C) {
+    Dw2Geom g;
+    const int half = C / 2;
+    if (C % 4 != 0 || half <= 0) return g;
+    g.gthreads = ((half + 31) / 32) * 32;
+    if (g.gthreads <= 192) g.NT = 192;
+    else if (g.gthreads <= 384) g.NT = 384;
+    else return g;
+    g.G = g.NT / g.gthreads;
+    if (g.G > cpn::DW2_MAXG) g.G = cpn::DW2_MAXG;
+    // Measured on B200 (profiles/r01_dwconv_notes.md): this kernel beats the register-marching LDG kernel only for
+    // one strip of 192 channel pairs per CTA (C = 384); the other widths keep the older kernel for now.
+    if (!(g.NT == 192 && g.G == 1) && getenv("CPN_DW_TMA_ALL") == nullptr) return g;
+    g.CB = C;
+    while (g.CB > 256 || C % g.CB != 0 || g.CB % 4 != 0) {
+        --g.CB;
+        if (g.CB < 4) return g;
+    }
+    g.nbox = C / g.CB;
+    const int tw_max = g.NT == 384 ? 2 : 4;  // 384 threads leave 168 registers per thread
+    double best = 1e30;
+    for (int tw = tw_max; tw >= 2; --tw) {
+        for (int chunks = 1; chunks <= 3; ++chunks) {
+            const int cols = g.G * tw;
+            const int strips = (W + cols - 1) / cols;
+            const int rows = (H + chunks - 1) / chunks;
+            const int in_rows = chunks == 1 ? H : rows + 6;
+            const long long ctas = static_cast<long long>(strips) * chunks * B;
+            const long long waves = (ctas + num_sms() - 1) / num_sms();
+            const double cost = static_cast<double>(waves) * (in_rows + 2) * tw * (1.0 + 0.05 * (4 - tw));
+            if (cost < best) { best = cost; g.TW = tw; g.chunks = chunks; }
+        }
+    }
+    const int ntok = g.G * g.TW + 6;
+    if (ntok > 256) return g;
+    g.box_bytes = ((ntok * g.CB * 4 + 127) / 128) * 128;
+    g.stage_bytes = g.nbox * g.box_bytes;
+    const size_t fixed = static_cast<size_t>(cpn::DW2_NSTAT) * cpn::DW2_MAXG * 8 * 4 +
+                         (2 * cpn::DW2_MAX_STAGES + cpn::DW2_NSTAT) * 8 + 128;
+    g.nst = cpn::DW2_MAX_STAGES;
+    while (g.nst > 2 && g.nst * static_cast<size_t>(g.stage_bytes) + fixed > 200 * 1024) --g.nst;
+    g.smem = g.nst * static_cast<size_t>(g.stage_bytes) + fixed;
+    g.ok = g.smem <= 200 * 1024;
+    return g;
+}
+
+template <int TW, int NT>
+int launch_dw2_inst(const CUtensorMap& tm, const cpn::Dw2Params& p, dim3 grid, size_t smem, cudaStream_t st) {
+    auto kern = cpn::dwconv7_ln_tma_kernel<TW, NT>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_done = true;
+    }
+    kern<<<grid, NT, smem, st>>>(tm, p);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, dim3 grid, size_t smem, cudaStream_t st) {
+    if (nt == 384) return launch_dw2_inst<2, 384>(tm, p, grid, smem, st);
+    switch (tw) {
+        case 2: return launch_dw2_inst<2, 192>(tm, p, grid, smem, st);
+        case 3: return launch_dw2_inst<3, 192>(tm, p, grid, smem, st);
+        default: return launch_dw2_inst<4, 192>(tm, p, grid, smem, st);
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -290,6 +392,30 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
                    void* stream) {
     if (C % 2 != 0 || C > 2 * 32 * cpn::DW_MAX_WARPS) return fail("cpn_dwconv7_ln: unsupported C=%d", C);
     if (B <= 0 || B > 65535) return fail("cpn_dwconv7_ln: unsupported B=%d", B);
+    {
+        const Dw2Geom g = dw2_geometry(B, H, W, C);
+        if (g.ok) {
+            CUtensorMap tm;
+            if (make_tmap_nhwc_f32(&tm, x, B, H, W, C, g.CB, g.G * g.TW + 6) != 0) return -1;
+            cpn::Dw2Params p;
+            p.w49 = w49; p.bias = bias; p.ln_w = ln_w; p.ln_b = ln_b;
+            p.out_hi = static_cast<__nv_bfloat16*>(out_hi);
+            p.out_lo = static_cast<__nv_bfloat16*>(out_lo);
+            p.H = H; p.W = W; p.C = C; p.G = g.G; p.gthreads = g.gthreads; p.CB = g.CB; p.nbox = g.nbox;
+            p.box_bytes = g.box_bytes; p.stage_bytes = g.stage_bytes; p.nst = g.nst;
+            p.rows_per_cta = (H + g.chunks - 1) / g.chunks; p.eps = eps;
+            const int cols = g.G * g.TW;
+            const dim3 grid((W + cols - 1) / cols, (H + p.rows_per_cta - 1) / p.rows_per_cta, B);
+            const size_t smem = g.smem;
+            const int tw = g.TW, nt = g.NT;
+            set_info("dwconv7_ln", 2.0 * 49 * B * H * W * C, 1.0 * B * H * W * C * (4 + 2 + (out_lo != nullptr ? 2 : 0)),
+                     "B=%d H=%d W=%d C=%d tma NT=%d G=%d TW=%d chunks=%d nst=%d", B, H, W, C, g.NT, g.G, g.TW, g.chunks,
+                     g.nst);
+            return submit(plan, stream, [=](cudaStream_t st) -> int {
+                return launch_dw2(tw, nt, tm, p, grid, smem, st);
+            });
+        }
+    }
     const int threads = ((C / 2 + 31) / 32) * 32;
     const int tw = (threads > 192) ? 2 : 4;
     // rows per CTA: whole column strips when the batch already fills the machine, shorter segments otherwise

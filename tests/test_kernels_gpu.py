@@ -106,7 +106,8 @@ def test_stem_ln(cuda_device):
     assert (out - ref).abs().max().item() < 2e-4
 
 
-@pytest.mark.parametrize("B,H,W,C", [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192)])
+@pytest.mark.parametrize("B,H,W,C", [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192),
+                                     (2, 56, 56, 96), (1, 54, 55, 384), (70, 7, 6, 96), (1, 3, 2, 64), (2, 13, 13, 40)])
 def test_dwconv7_ln(cuda_device, B, H, W, C):
     g = torch.Generator().manual_seed(C + H)
     x = torch.randn(B, H, W, C, generator=g).to(cuda_device)

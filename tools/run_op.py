@@ -1,0 +1,62 @@
+#!/usr/bin/env python
+"""Runs one C-ABI kernel alone at a benchmark shape (for ncu captures and CUDA-event timing).
+    python tools/run_op.py dwconv --B 64 --H 27 --W 27 --C 384 [--iters 5]
+    python tools/run_op.py gemm --M 46656 --N 1536 --K 384 --act 1 [--res 1]
+"""
+import argparse
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from count_pipnet_b200 import _lib, ops  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("op")
+    for k, d in dict(B=64, H=27, W=27, C=384, M=46656, N=1536, K=384, act=0, res=0, iters=5).items():
+        ap.add_argument("--" + k, type=int, default=d)
+    a = ap.parse_args()
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(0)
+    if a.op == "dwconv":
+        x = torch.randn(a.B, a.H, a.W, a.C, generator=g).to(dev)
+        w49 = (torch.randn(49, a.C, generator=g) * 0.2).to(dev)
+        b, lw, lb = (torch.randn(a.C, generator=g).to(dev) for _ in range(3))
+        out = torch.empty(a.B * a.H * a.W, a.C, device=dev, dtype=torch.bfloat16)
+        fn = lambda: ops.dwconv7_ln(x, w49, b, lw, lb, out)
+        nbytes = x.numel() * 4 + out.numel() * 2
+        flops = 2.0 * 49 * x.numel()
+    elif a.op == "gemm":
+        A = torch.randn(a.M, a.K, generator=g).to(dev).to(torch.bfloat16)
+        Wt = (torch.randn(a.N, a.K, generator=g) / a.K ** 0.5).to(dev).to(torch.bfloat16)
+        bias = torch.randn(a.N, generator=g).to(dev)
+        if a.res:
+            res = torch.randn(a.M, a.N, generator=g).to(dev)
+            scale = torch.rand(a.N, generator=g).to(dev)
+            fn = lambda: ops.gemm_bf16(A, Wt, a.M, a.N, a.K, bias=bias, scale=scale, res_f32=res, out_f32=res)
+            nbytes = A.numel() * 2 + Wt.numel() * 2 + res.numel() * 8
+        else:
+            out = torch.empty(a.M, a.N, device=dev, dtype=torch.bfloat16)
+            fn = lambda: ops.gemm_bf16(A, Wt, a.M, a.N, a.K, bias=bias, out_bf16=out, act=a.act)
+            nbytes = A.numel() * 2 + Wt.numel() * 2 + out.numel() * 2
+        flops = 2.0 * a.M * a.N * a.K
+    else:
+        raise SystemExit("unknown op")
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / a.iters
+    print(f"{a.op} {vars(a)}: {ms:.4f} ms  {flops / ms / 1e9:.1f} TFLOP/s  {nbytes / ms / 1e6:.1f} GB/s")
+
+
+if __name__ == "__main__":
+    main()
