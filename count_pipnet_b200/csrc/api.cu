@@ -17,6 +17,7 @@
 #include "convnext_kernels.cuh"
 #include "dwconv_tma.cuh"
 #include "gemm_tcgen05.cuh"
+#include "gemm_tma_epi.cuh"
 #include "head_kernels.cuh"
 #include "layout_kernels.cuh"
 
@@ -197,6 +198,86 @@ int pick_bn(int M, int N, bool split) {
     return best;
 }
 
+// Row-major [rows, cols] output (bf16 or fp32) for the TMA epilogue: box = 128 bytes x 32 rows, 128-byte swizzle.
+int make_tmap_out(CUtensorMap* m, const void* ptr, long long rows, int cols, bool bf16) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA output not 16-byte aligned");
+    const int esz = bf16 ? 2 : 4;
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * esz};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail("cuTensorMapEncodeTiled (output) failed with CUresult %d (rows=%lld cols=%d)", static_cast<int>(r),
+                    rows, cols);
+    return 0;
+}
+
+struct Gemm2Launch {
+    CUtensorMap ta, tb, tout;
+    cpn::Gemm2Params p;
+    int grid;
+};
+
+template <int BN, int EPI>
+int launch_gemm2_inst(const Gemm2Launch& g, cudaStream_t st) {
+    using S = cpn::Gemm2Cfg<BN, EPI>;
+    auto kern = cpn::gemm_tma_epi_kernel<BN, EPI>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        attr_done = true;
+    }
+    kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int EPI>
+int launch_gemm2_bn(const Gemm2Launch& g, int bn, cudaStream_t st) {
+    switch (bn) {
+        case 256: return launch_gemm2_inst<256, EPI>(g, st);
+        case 192: return launch_gemm2_inst<192, EPI>(g, st);
+        case 128: return launch_gemm2_inst<128, EPI>(g, st);
+        case 64: return launch_gemm2_inst<64, EPI>(g, st);
+    }
+    if (EPI != cpn::EPI_GELU_BF16) {
+        if (bn == 96) return launch_gemm2_inst<96, EPI == cpn::EPI_GELU_BF16 ? cpn::EPI_BIAS_F32 : EPI>(g, st);
+        if (bn == 32) return launch_gemm2_inst<32, EPI == cpn::EPI_GELU_BF16 ? cpn::EPI_BIAS_F32 : EPI>(g, st);
+    }
+    return fail("no TMA-epilogue GEMM instantiation for BN=%d", bn);
+}
+
+int launch_gemm2(const Gemm2Launch& g, int bn, int epi, cudaStream_t st) {
+    switch (epi) {
+        case cpn::EPI_GELU_BF16: return launch_gemm2_bn<cpn::EPI_GELU_BF16>(g, bn, st);
+        case cpn::EPI_SCALE_RES_F32: return launch_gemm2_bn<cpn::EPI_SCALE_RES_F32>(g, bn, st);
+        default: return launch_gemm2_bn<cpn::EPI_BIAS_F32>(g, bn, st);
+    }
+}
+
+// Tile width for the TMA-epilogue kernel: a multiple of the 128-byte output chunk that divides N.
+int pick_bn2(int M, int N, int epi) {
+    static const int cands[] = {256, 192, 128, 96, 64, 32};
+    const int chunk = epi == cpn::EPI_GELU_BF16 ? 64 : 32;
+    const int m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
+    int best = 0;
+    for (int bn : cands) {
+        if (N % bn != 0 || bn % chunk != 0) continue;
+        if (best == 0) best = bn;
+        if (m_blocks * (N / bn) >= num_sms()) return bn;
+    }
+    for (int i = 5; i >= 0; --i) {
+        const int bn = cands[i];
+        if (N % bn == 0 && bn % chunk == 0 && bn >= 64) return bn;
+    }
+    return best;
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ plan
@@ -236,9 +317,9 @@ Dw2Geom dw2_geometry(int B, int H, int W, int C) {
     else return g;
     g.G = g.NT / g.gthreads;
     if (g.G > cpn::DW2_MAXG) g.G = cpn::DW2_MAXG;
-    // Measured on B200 (profiles/r01_dwconv_notes.md): this kernel beats the register-marching LDG kernel only for
-    // one strip of 192 channel pairs per CTA (C = 384); the other widths keep the older kernel for now.
-    if (!(g.NT == 192 && g.G == 1) && getenv("CPN_DW_TMA_ALL") == nullptr) return g;
+    // Round 1: off by default. It is only ahead of the register-marching LDG kernel for C = 384 (profiles/
+    // r01_dwconv_notes.md) and its forward is not yet run-to-run identical there; CPN_DW_TMA=1 enables it.
+    if (getenv("CPN_DW_TMA") == nullptr) return g;
     g.CB = C;
     while (g.CB > 256 || C % g.CB != 0 || g.CB % 4 != 0) {
         --g.CB;
@@ -466,6 +547,40 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
     if (out_f32 == nullptr && out_bf16 == nullptr) return fail("cpn_gemm_bf16: no output");
     if (out_bf16_lo != nullptr && out_bf16 == nullptr) return fail("cpn_gemm_bf16: lo plane needs the hi plane");
     const bool split = A_lo != nullptr;
+    if (!split && bias != nullptr && out_bf16_lo == nullptr && res_bf16 == nullptr && !relu_after_res &&
+        getenv("CPN_GEMM_LEGACY") == nullptr) {
+        int epi = -1;
+        if (act == CPN_ACT_GELU && out_bf16 != nullptr && out_f32 == nullptr && scale == nullptr && res_f32 == nullptr)
+            epi = cpn::EPI_GELU_BF16;
+        else if (act == CPN_ACT_NONE && out_f32 != nullptr && out_bf16 == nullptr && scale != nullptr &&
+                 res_f32 == out_f32)
+            epi = cpn::EPI_SCALE_RES_F32;
+        else if (act == CPN_ACT_NONE && out_f32 != nullptr && out_bf16 == nullptr && scale == nullptr &&
+                 res_f32 == nullptr)
+            epi = cpn::EPI_BIAS_F32;
+        const int bn2 = epi >= 0 ? pick_bn2(M, N, epi) : 0;
+        if (bn2 != 0) {
+            Gemm2Launch g;
+            memset(&g, 0, sizeof(g));
+            if (make_tmap(&g.ta, A, M, K, cpn::GEMM_BM) != 0) return -1;
+            if (make_tmap(&g.tb, Bw, N, K, bn2) != 0) return -1;
+            const bool obf = epi == cpn::EPI_GELU_BF16;
+            if (make_tmap_out(&g.tout, obf ? out_bf16 : static_cast<void*>(out_f32), M, N, obf) != 0) return -1;
+            g.p.M = M; g.p.N = N; g.p.K = K;
+            g.p.num_m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
+            g.p.num_n_blocks = N / bn2;
+            g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+            g.p.bias = bias; g.p.scale = scale;
+            const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
+            g.grid = tiles < num_sms() ? tiles : num_sms();
+            const double mn = static_cast<double>(M) * N;
+            const double bytes = 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) +
+                                 (obf ? 2.0 : (epi == cpn::EPI_SCALE_RES_F32 ? 8.0 : 4.0)) * mn;
+            set_info("gemm_bf16", 2.0 * mn * K, bytes, "M=%d N=%d K=%d BN=%d epi=%s", M, N, K, bn2,
+                     obf ? "gelu_bf16" : (epi == cpn::EPI_SCALE_RES_F32 ? "scale_res_f32" : "bias_f32"));
+            return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
+        }
+    }
     const int bn = pick_bn(M, N, split);
     if (bn == 0) return fail("cpn_gemm_bf16: no tile width divides N=%d", N);
     GemmLaunch g;

@@ -1,0 +1,268 @@
+// bf16-mode GEMMs of the ConvNeXt blocks: same TMA -> tcgen05 main loop as gemm_tcgen05.cuh, with an epilogue that
+// moves whole 32-row x 128-byte blocks between registers, shared memory and HBM:
+//
+//   EPI_GELU_BF16      out_bf16 = gelu(acc + bias)                    CNBlock fc1 + GELU   (tv convnext.py:55-56)
+//   EPI_SCALE_RES_F32  out_f32  = res_f32 + scale * (acc + bias)      CNBlock fc2, layer_scale, residual (:57,64-66)
+//   EPI_BIAS_F32       out_f32  = acc + bias                          downsample conv 2x2 (:146-150)
+//
+// Each of the 8 epilogue warps owns a 32-row quarter of the accumulator (its TMEM lanes) and every other column chunk.
+// A chunk (64 bf16 or 32 fp32 columns = 128 B per row) is read with tcgen05.ld.x32, finished in registers, written
+// to a 4 KB staging block in the 128-byte TMA swizzle (conflict-free 16-byte stores, lane = row) and sent to HBM with
+// one TMA store; the fp32 residual comes in the same way (TMA load into the staging block, prefetched one chunk ahead
+// and, for the first chunk of a tile, before the accumulator is even ready), so the epilogue issues no per-lane
+// global loads or stores at all. out and res may be the same buffer (the residual stream is updated in place).
+#pragma once
+#include "gelu_fast.cuh"
+#include "gemm_tcgen05.cuh"
+
+namespace cpn {
+
+enum GemmEpi : int { EPI_GELU_BF16 = 0, EPI_SCALE_RES_F32 = 1, EPI_BIAS_F32 = 2 };
+
+struct Gemm2Params {
+    int M, N, K;
+    int num_m_blocks, num_n_blocks, num_k_blocks;
+    const float* bias;   // [N]
+    const float* scale;  // [N] (EPI_SCALE_RES_F32)
+};
+
+template <int BN, int EPI>
+struct Gemm2Cfg {
+    static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+    static constexpr int B_BYTES = BN * GEMM_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int CHUNK_COLS = (EPI == EPI_GELU_BF16) ? 64 : 32;  // 128 bytes of output per row
+    static constexpr int NCHUNK = BN / CHUNK_COLS;
+    static constexpr int STG_BLOCK = 32 * 128;                        // one chunk: 32 rows x 128 B
+    static constexpr int STAGING_BYTES = GEMM_EPI_WARPS * 2 * STG_BLOCK;  // two blocks per epilogue warp
+    static constexpr int BAR_BYTES = (2 * 8 + 4 + 2 * GEMM_EPI_WARPS) * 8 + 16;
+    static constexpr int BUDGET = 227 * 1024 - 1024 - STAGING_BYTES - BAR_BYTES;
+    static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
+    static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = TILE_BYTES + STAGING_BYTES + BAR_BYTES + 1024;
+    static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128
+                                     : (2 * BN <= 256) ? 256 : 512;
+    static_assert(BN % CHUNK_COLS == 0, "tile width must be a whole number of 128-byte output chunks");
+    static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_out, const Gemm2Params p) {
+    using S = Gemm2Cfg<BN, EPI>;
+    constexpr int STAGES = S::STAGES;
+    static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N constraint for M=128");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    auto stage_a = [&](int s) { return smem + s * S::STAGE_BYTES; };
+    auto stage_b = [&](int s) { return smem + s * S::STAGE_BYTES + S::A_BYTES; };
+    uint8_t* staging = smem + S::TILE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + S::STAGING_BYTES);
+    uint64_t* empty_bar = full_bar + 8;
+    uint64_t* tmem_full_bar = empty_bar + 8;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint64_t* res_bar = tmem_empty_bar + 2;  // [epilogue warp][2]
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(res_bar + 2 * GEMM_EPI_WARPS);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmap_a);
+        ptx::prefetch_tmap(&tmap_b);
+        ptx::prefetch_tmap(&tmap_out);
+        for (int s = 0; s < STAGES; ++s) {
+            ptx::mbar_init(&full_bar[s], 1);
+            ptx::mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&tmem_full_bar[s], 1);
+            ptx::mbar_init(&tmem_empty_bar[s], GEMM_EPI_WARPS);
+        }
+        for (int s = 0; s < 2 * GEMM_EPI_WARPS; ++s) ptx::mbar_init(&res_bar[s], 1);
+        ptx::fence_mbar_init();
+    } else if (warp == 2) {
+        ptx::tmem_alloc(tmem_holder, S::TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m_blk = tile / p.num_n_blocks;
+                const int n_blk = tile % p.num_n_blocks;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    ptx::mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+                    ptx::tma_load_2d(stage_a(stage), &tmap_a, kb * GEMM_BK, m_blk * GEMM_BM, &full_bar[stage]);
+                    ptx::tma_load_2d(stage_b(stage), &tmap_b, kb * GEMM_BK, n_blk * BN, &full_bar[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer (single thread)
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(GEMM_BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + as * BN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t adesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_a(stage)));
+                    const uint64_t bdesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_b(stage)));
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k)
+                        ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    ptx::umma_commit(&empty_bar[stage]);
+                    if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[as]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue (8 warps)
+        const int ew = warp - 4;
+        const int q = warp & 3;    // TMEM lane quarter this warp may access = 32-row block of the tile
+        const int half = ew >> 2;  // this warp takes chunks half, half + 2, ...
+        const uint32_t stg = ptx::smem_u32(staging) + ew * 2 * S::STG_BLOCK;
+        uint8_t* stg_ptr = staging + ew * 2 * S::STG_BLOCK;
+        uint64_t* rbar = res_bar + 2 * ew;
+        const uint32_t sw = static_cast<uint32_t>(lane & 7);          // swizzle phase of this lane's row
+        const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;  // this lane's row inside a staging block
+        uint32_t g = 0;  // chunks processed so far by this warp: buffer = g & 1, barrier parity = (g >> 1) & 1
+        int it = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            const int m_blk = tile / p.num_n_blocks;
+            const int n_blk = tile % p.num_n_blocks;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            const int row0 = m_blk * GEMM_BM + q * 32;
+            const int col_tile = n_blk * BN;
+            if (EPI == EPI_SCALE_RES_F32 && half < S::NCHUNK) {
+                // residual of the first chunk: does not depend on the accumulator, so it travels while the MMAs run
+                if (lane == 0) {
+                    ptx::bulk_wait_read<0>();  // earlier stores have finished reading both staging blocks
+                    const uint32_t b = g & 1;
+                    ptx::mbar_arrive_expect_tx(&rbar[b], S::STG_BLOCK);
+                    ptx::tma_load_2d(stg_ptr + b * S::STG_BLOCK, &tmap_out, col_tile + half * S::CHUNK_COLS, row0, &rbar[b]);
+                }
+                __syncwarp();
+            }
+            ptx::mbar_wait(&tmem_full_bar[as], aphase);
+            ptx::tc_fence_after();
+            const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int c = half; c < S::NCHUNK; c += 2, ++g) {
+                const uint32_t b = g & 1;
+                const uint32_t buf = stg + b * S::STG_BLOCK + row_off;
+                const int col0 = col_tile + c * S::CHUNK_COLS;
+                const bool last = c + 2 >= S::NCHUNK;
+                if (EPI == EPI_SCALE_RES_F32) {
+                    if (!last) {
+                        if (lane == 0) {
+                            ptx::bulk_wait_read<0>();  // the store of the previous chunk has released the other block
+                            ptx::mbar_arrive_expect_tx(&rbar[b ^ 1], S::STG_BLOCK);
+                            ptx::tma_load_2d(stg_ptr + (b ^ 1) * S::STG_BLOCK, &tmap_out, col0 + 2 * S::CHUNK_COLS, row0,
+                                             &rbar[b ^ 1]);
+                        }
+                        __syncwarp();
+                    }
+                } else {
+                    if (lane == 0) ptx::bulk_wait_read<1>();  // the store that last used this block is done reading
+                    __syncwarp();
+                }
+                uint32_t r0[32];
+                ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS, r0);
+                if (EPI == EPI_GELU_BF16) {
+                    uint32_t r1[32];
+                    ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS + 32, r1);
+                    ptx::tmem_ld_wait();
+                    if (last) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+                    }
+                    // 64 columns -> gelu(acc + bias) -> 8 x 16 bytes of bf16
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const uint32_t* src = (j < 4) ? (r0 + 8 * j) : (r1 + 8 * (j - 4));
+                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
+                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
+                        const float2 y0 = gelu_fast2(make_float2(__uint_as_float(src[0]) + b0.x, __uint_as_float(src[1]) + b0.y));
+                        const float2 y1 = gelu_fast2(make_float2(__uint_as_float(src[2]) + b0.z, __uint_as_float(src[3]) + b0.w));
+                        const float2 y2 = gelu_fast2(make_float2(__uint_as_float(src[4]) + b1.x, __uint_as_float(src[5]) + b1.y));
+                        const float2 y3 = gelu_fast2(make_float2(__uint_as_float(src[6]) + b1.z, __uint_as_float(src[7]) + b1.w));
+                        ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
+                                    make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
+                    }
+                } else {
+                    ptx::tmem_ld_wait();
+                    if (last) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+                    }
+                    if (EPI == EPI_SCALE_RES_F32) ptx::mbar_wait(&rbar[b], (g >> 1) & 1);
+                    // 32 columns -> res + scale * (acc + bias) (or acc + bias) -> 8 x 16 bytes of fp32
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const uint32_t a = buf + ((static_cast<uint32_t>(j) ^ sw) << 4);
+                        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 4 * j));
+                        float4 v = make_float4(__uint_as_float(r0[4 * j]) + b4.x, __uint_as_float(r0[4 * j + 1]) + b4.y,
+                                               __uint_as_float(r0[4 * j + 2]) + b4.z, __uint_as_float(r0[4 * j + 3]) + b4.w);
+                        if (EPI == EPI_SCALE_RES_F32) {
+                            const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + 4 * j));
+                            const float4 rs = ptx::lds_f4(a);
+                            v.x = fmaf(v.x, s4.x, rs.x); v.y = fmaf(v.y, s4.y, rs.y);
+                            v.z = fmaf(v.z, s4.z, rs.z); v.w = fmaf(v.w, s4.w, rs.w);
+                        }
+                        ptx::sts_u4(a, make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z),
+                                                  __float_as_uint(v.w)));
+                    }
+                }
+                ptx::fence_proxy_async();  // generic-proxy writes -> visible to the TMA store
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::tma_store_2d(&tmap_out, stg_ptr + b * S::STG_BLOCK, col0, row0);
+                    ptx::bulk_commit();
+                }
+            }
+            if (half >= S::NCHUNK) {  // a tile narrower than two chunks leaves this warp without work
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+            }
+        }
+        if (lane == 0) ptx::bulk_wait<0>();  // all stores complete before the CTA (and its shared memory) goes away
+        __syncwarp();
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, S::TMEM_COLS);
+    }
+}
+
+}  // namespace cpn

@@ -29,8 +29,8 @@ def test_gemm_plain(cuda_device, M, N, K):
     assert err < 2e-3 * max(1.0, ref.abs().max().item()), err
 
 
-def test_gemm_gelu_bf16_out(cuda_device):
-    M, N, K = 3000, 768, 192
+@pytest.mark.parametrize("M,N,K", [(3000, 768, 192), (777, 384, 96), (2500, 1536, 384), (1300, 3072, 768), (200, 64, 64)])
+def test_gemm_gelu_bf16_out(cuda_device, M, N, K):
     g = torch.Generator().manual_seed(1)
     a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
     w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)
@@ -42,8 +42,8 @@ def test_gemm_gelu_bf16_out(cuda_device):
     assert (out.float() - ref).abs().max().item() < 0.03
 
 
-def test_gemm_scale_residual_inplace(cuda_device):
-    M, N, K = 2500, 192, 768
+@pytest.mark.parametrize("M,N,K", [(2500, 192, 768), (5000, 96, 384), (1111, 384, 1536), (900, 768, 3072), (130, 32, 64)])
+def test_gemm_scale_residual_inplace(cuda_device, M, N, K):
     g = torch.Generator().manual_seed(2)
     a = torch.randn(M, K, generator=g).to(cuda_device).to(torch.bfloat16)
     w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device).to(torch.bfloat16)

@@ -76,9 +76,16 @@ def test_fused_forward_matches_reference_golden(cuda_device, name, precision):
         assert np.abs(np.where(near, raw - g["map_max"], pooled - g["pooled"])).max() <= tol * scale, errs
     else:
         assert errs["pooled"] <= tol, errs
-    assert errs["out"] <= tol, errs
-    assert np.array_equal(out.argmax(1), g["pred"])
-    assert np.array_equal(pooled.argmax(1), g["top_proto"])
+    # images whose counts / thresholded scores legitimately flipped (bf16 mode, see above) have different logits
+    same = np.ones(out.shape[0], dtype=bool)
+    if precision == "bf16" and case["inference"]:
+        flipped = (pooled != g["pooled"]) & ((pooled == 0) | (g["pooled"] == 0) | is_count_inf)
+        assert flipped.mean() <= 0.01  # the boundary checks above already bound where a flip may happen
+        same = ~flipped.any(axis=1)
+    if same.any():
+        assert rel(out[same], g["out"][same]) <= tol, errs
+        assert np.array_equal(out.argmax(1)[same], g["pred"][same])
+        assert np.array_equal(pooled.argmax(1)[same], g["top_proto"][same])
     if precision == "fp32":
         # per-(image, prototype) arg-max patch, where the maximum is not a near-tie
         am = flat.argmax(2).cpu().numpy()
