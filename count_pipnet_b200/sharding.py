@@ -1,0 +1,50 @@
+"""Batch sharding of the forward path across the GPUs of one box.
+
+The reference's only parallelism is nn.DataParallel (main.py:118): contiguous batch chunks per device, outputs
+concatenated in device order. Here every rank (one process per GPU) owns the same contiguous chunk DataParallel would
+give it and runs the whole path on it; the one exchange step is the all-gather of the small per-image outputs
+(logits [b, K], pooled scores or counts [b, P]). The patch x prototype map stays on the rank that produced it.
+Works with any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(batch: int, world: int) -> List[Tuple[int, int]]:
+    """[start, end) of every rank's chunk, the split torch.nn.parallel.scatter (tensor.chunk) makes: chunks of
+    ceil(batch / world) images, the last ones shorter or empty."""
+    per = -(-batch // world) if world > 0 else batch
+    out = []
+    for r in range(world):
+        s = min(r * per, batch)
+        out.append((s, min(s + per, batch)))
+    return out
+
+
+def my_shard(x: torch.Tensor, rank: Optional[int] = None, world: Optional[int] = None) -> torch.Tensor:
+    rank = dist.get_rank() if rank is None else rank
+    world = dist.get_world_size() if world is None else world
+    s, e = shard_bounds(x.shape[0], world)[rank]
+    return x[s:e]
+
+
+def gather_outputs(pooled: torch.Tensor, out: torch.Tensor, batch: int, group=None):
+    """All-gather the per-image outputs of every rank into full-batch tensors (reference row order). Ragged shards
+    are padded to the largest chunk for the collective and trimmed afterwards."""
+    world = dist.get_world_size(group)
+    bounds = shard_bounds(batch, world)
+    per = max(e - s for s, e in bounds)
+
+    def gather(t: torch.Tensor) -> torch.Tensor:
+        pad = t.new_zeros((per,) + tuple(t.shape[1:]))
+        pad[: t.shape[0]] = t
+        full = t.new_empty((world * per,) + tuple(t.shape[1:]))
+        dist.all_gather_into_tensor(full, pad, group=group) if hasattr(dist, "all_gather_into_tensor") and t.is_cuda \
+            else dist.all_gather(list(full.split(per)), pad, group=group)
+        return torch.cat([full[r * per: r * per + (e - s)] for r, (s, e) in enumerate(bounds)], dim=0)
+
+    return gather(pooled), gather(out)
