@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "convnext_kernels.cuh"
+#include "dwconv_stats.cuh"
 #include "dwconv_tma.cuh"
 #include "gemm_tcgen05.cuh"
 #include "gemm_tma_epi.cuh"
@@ -245,9 +246,9 @@ int launch_gemm2_bn(const Gemm2Launch& g, int bn, cudaStream_t st) {
         case 128: return launch_gemm2_inst<128, EPI>(g, st);
         case 64: return launch_gemm2_inst<64, EPI>(g, st);
     }
-    if (EPI != cpn::EPI_GELU_BF16) {
-        if (bn == 96) return launch_gemm2_inst<96, EPI == cpn::EPI_GELU_BF16 ? cpn::EPI_BIAS_F32 : EPI>(g, st);
-        if (bn == 32) return launch_gemm2_inst<32, EPI == cpn::EPI_GELU_BF16 ? cpn::EPI_BIAS_F32 : EPI>(g, st);
+    if (!cpn::epi_out_bf16(EPI)) {
+        if (bn == 96) return launch_gemm2_inst<96, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI>(g, st);
+        if (bn == 32) return launch_gemm2_inst<32, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI>(g, st);
     }
     return fail("no TMA-epilogue GEMM instantiation for BN=%d", bn);
 }
@@ -256,6 +257,7 @@ int launch_gemm2(const Gemm2Launch& g, int bn, int epi, cudaStream_t st) {
     switch (epi) {
         case cpn::EPI_GELU_BF16: return launch_gemm2_bn<cpn::EPI_GELU_BF16>(g, bn, st);
         case cpn::EPI_SCALE_RES_F32: return launch_gemm2_bn<cpn::EPI_SCALE_RES_F32>(g, bn, st);
+        case cpn::EPI_LN_GELU_BF16: return launch_gemm2_bn<cpn::EPI_LN_GELU_BF16>(g, bn, st);
         default: return launch_gemm2_bn<cpn::EPI_BIAS_F32>(g, bn, st);
     }
 }
@@ -263,7 +265,7 @@ int launch_gemm2(const Gemm2Launch& g, int bn, int epi, cudaStream_t st) {
 // Tile width for the TMA-epilogue kernel: a multiple of the 128-byte output chunk that divides N.
 int pick_bn2(int M, int N, int epi) {
     static const int cands[] = {256, 192, 128, 96, 64, 32};
-    const int chunk = epi == cpn::EPI_GELU_BF16 ? 64 : 32;
+    const int chunk = cpn::epi_out_bf16(epi) ? 64 : 32;
     const int m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
     int best = 0;
     for (int bn : cands) {
@@ -375,6 +377,16 @@ int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, d
     }
 }
 
+}  // namespace
+
+namespace {
+template <int C>
+int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
+               int nstrips, int rows, dim3 grid, cudaStream_t st) {
+    cpn::dwconv7_stats_kernel<C, 4><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
 }  // namespace
 
 extern "C" {
@@ -516,6 +528,62 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
         CPN_CUDA(cudaGetLastError());
         return 0;
     });
+}
+
+int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
+                      float* stats, int B, int H, int W, int C, void* stream) {
+    if (C != 96 && C != 192 && C != 384 && C != 768)
+        return fail("cpn_dwconv7_stats: C=%d is not a ConvNeXt-tiny width (96, 192, 384, 768)", C);
+    if (B <= 0 || B > 65535 || H <= 0 || W <= 0) return fail("cpn_dwconv7_stats: bad shape B=%d H=%d W=%d", B, H, W);
+    const int nstrips = (W + 3) / 4;
+    const int units = nstrips * (C / 32);
+    const int gx = (units + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
+    // row segments: enough CTAs for >= 4 waves of 4 CTAs per SM, but segments no shorter than 7 rows
+    int nseg = 1;
+    while (static_cast<long long>(gx) * nseg * B < 16LL * num_sms() && (H + nseg) / (nseg + 1) >= 7) ++nseg;
+    const int rows = (H + nseg - 1) / nseg;
+    nseg = (H + rows - 1) / rows;
+    const dim3 grid(gx, nseg, B);
+    auto* out = static_cast<__nv_bfloat16*>(out_bf16);
+    const double tok = static_cast<double>(B) * H * W;
+    set_info("dwconv7_stats", 2.0 * 49 * tok * C, tok * C * (4 + 2) + tok * (C / 32) * 8, "B=%d H=%d W=%d C=%d rows/seg=%d",
+             B, H, W, C, rows);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        switch (C) {
+            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+        }
+    });
+}
+
+int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N, int K, const float* stats,
+                     int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream) {
+    if (M <= 0 || N <= 0 || K <= 0) return fail("cpn_gemm_ln_gelu: bad shape M=%d N=%d K=%d", M, N, K);
+    if (K % 8 != 0) return fail("cpn_gemm_ln_gelu: K must be a multiple of 8, K=%d", K);
+    if (nparts <= 0 || stats == nullptr || colsum == nullptr || bias == nullptr || out_bf16 == nullptr)
+        return fail("cpn_gemm_ln_gelu: missing operand");
+    const int epi = cpn::EPI_LN_GELU_BF16;
+    const int bn2 = pick_bn2(M, N, epi);
+    if (bn2 == 0 || bn2 == 96 || bn2 == 32) return fail("cpn_gemm_ln_gelu: no tile width for N=%d", N);
+    Gemm2Launch g;
+    memset(&g, 0, sizeof(g));
+    if (make_tmap(&g.ta, A, M, K, cpn::GEMM_BM) != 0) return -1;
+    if (make_tmap(&g.tb, Bw, N, K, bn2) != 0) return -1;
+    if (make_tmap_out(&g.tout, out_bf16, M, N, true) != 0) return -1;
+    g.p.M = M; g.p.N = N; g.p.K = K;
+    g.p.num_m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
+    g.p.num_n_blocks = N / bn2;
+    g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+    g.p.bias = bias; g.p.scale = nullptr;
+    g.p.stats = stats; g.p.colsum = colsum; g.p.nparts = nparts; g.p.inv_k = 1.0f / static_cast<float>(K); g.p.eps = eps;
+    const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
+    g.grid = tiles < num_sms() ? tiles : num_sms();
+    const double mn = static_cast<double>(M) * N;
+    set_info("gemm_bf16", 2.0 * mn * K, 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) + 2.0 * mn,
+             "M=%d N=%d K=%d BN=%d epi=ln_gelu_bf16", M, N, K, bn2);
+    return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
 }
 
 int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const float* ln_b, void* out_hi, void* out_lo,

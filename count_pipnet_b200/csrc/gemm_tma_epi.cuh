@@ -4,6 +4,10 @@
 //   EPI_GELU_BF16      out_bf16 = gelu(acc + bias)                    CNBlock fc1 + GELU   (tv convnext.py:55-56)
 //   EPI_SCALE_RES_F32  out_f32  = res_f32 + scale * (acc + bias)      CNBlock fc2, layer_scale, residual (:57,64-66)
 //   EPI_BIAS_F32       out_f32  = acc + bias                          downsample conv 2x2 (:146-150)
+//   EPI_LN_GELU_BF16   out_bf16 = gelu(rstd_m * (acc - mean_m * colsum) + bias)   LayerNorm folded into fc1 (:53-56):
+//                      A holds the un-normalised depthwise-conv output, Bw = bf16(W1 * gamma), colsum[n] = sum_k Bw[n,k],
+//                      bias = b1 + W1 * beta; mean_m / rstd_m come from the per-token partial sums written by
+//                      dwconv7_stats_kernel (stats [M, nparts, 2]), summed here in a fixed order.
 //
 // Each of the 8 epilogue warps owns a 32-row quarter of the accumulator (its TMEM lanes) and every other column chunk.
 // A chunk (64 bf16 or 32 fp32 columns = 128 B per row) is read with tcgen05.ld.x32, finished in registers, written
@@ -17,13 +21,20 @@
 
 namespace cpn {
 
-enum GemmEpi : int { EPI_GELU_BF16 = 0, EPI_SCALE_RES_F32 = 1, EPI_BIAS_F32 = 2 };
+enum GemmEpi : int { EPI_GELU_BF16 = 0, EPI_SCALE_RES_F32 = 1, EPI_BIAS_F32 = 2, EPI_LN_GELU_BF16 = 3 };
+__host__ __device__ constexpr bool epi_out_bf16(int epi) { return epi == EPI_GELU_BF16 || epi == EPI_LN_GELU_BF16; }
 
 struct Gemm2Params {
     int M, N, K;
     int num_m_blocks, num_n_blocks, num_k_blocks;
     const float* bias;   // [N]
     const float* scale;  // [N] (EPI_SCALE_RES_F32)
+    // EPI_LN_GELU_BF16
+    const float* stats;   // [M, nparts, 2] partial (sum, sum of squares) over the K = C channels of each token
+    const float* colsum;  // [N]
+    int nparts;
+    float inv_k;          // 1 / C
+    float eps;
 };
 
 template <int BN, int EPI>
@@ -31,7 +42,7 @@ struct Gemm2Cfg {
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
     static constexpr int B_BYTES = BN * GEMM_BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int CHUNK_COLS = (EPI == EPI_GELU_BF16) ? 64 : 32;  // 128 bytes of output per row
+    static constexpr int CHUNK_COLS = epi_out_bf16(EPI) ? 64 : 32;  // 128 bytes of output per row
     static constexpr int NCHUNK = BN / CHUNK_COLS;
     static constexpr int STG_BLOCK = 32 * 128;                        // one chunk: 32 rows x 128 B
     static constexpr int STAGING_BYTES = GEMM_EPI_WARPS * 2 * STG_BLOCK;  // two blocks per epilogue warp
@@ -168,6 +179,21 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 }
                 __syncwarp();
             }
+            float ln_rs = 1.f, ln_nm = 0.f;  // rstd and -mean * rstd of this lane's row
+            if (EPI == EPI_LN_GELU_BF16) {
+                const int row = min(row0 + lane, p.M - 1);
+                const float2* sp = reinterpret_cast<const float2*>(p.stats) + static_cast<size_t>(row) * p.nparts;
+                float s1 = 0.f, s2 = 0.f;
+                for (int i = 0; i < p.nparts; ++i) {
+                    const float2 v = __ldg(sp + i);
+                    s1 += v.x;
+                    s2 += v.y;
+                }
+                const float mean = s1 * p.inv_k;
+                const float var = fmaxf(s2 * p.inv_k - mean * mean, 0.f);
+                ln_rs = rsqrtf(var + p.eps);
+                ln_nm = -mean * ln_rs;
+            }
             ptx::mbar_wait(&tmem_full_bar[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -193,7 +219,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 }
                 uint32_t r0[32];
                 ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS, r0);
-                if (EPI == EPI_GELU_BF16) {
+                if (epi_out_bf16(EPI)) {
                     uint32_t r1[32];
                     ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS + 32, r1);
                     ptx::tmem_ld_wait();
@@ -206,12 +232,30 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const uint32_t* src = (j < 4) ? (r0 + 8 * j) : (r1 + 8 * (j - 4));
-                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
-                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
-                        const float2 y0 = gelu_fast2(make_float2(__uint_as_float(src[0]) + b0.x, __uint_as_float(src[1]) + b0.y));
-                        const float2 y1 = gelu_fast2(make_float2(__uint_as_float(src[2]) + b0.z, __uint_as_float(src[3]) + b0.w));
-                        const float2 y2 = gelu_fast2(make_float2(__uint_as_float(src[4]) + b1.x, __uint_as_float(src[5]) + b1.y));
-                        const float2 y3 = gelu_fast2(make_float2(__uint_as_float(src[6]) + b1.z, __uint_as_float(src[7]) + b1.w));
+                        float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
+                        float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
+                        float v[8];
+                        if (EPI == EPI_LN_GELU_BF16) {
+                            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j));
+                            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j + 4));
+                            b0.x = fmaf(ln_nm, s0.x, b0.x); b0.y = fmaf(ln_nm, s0.y, b0.y);
+                            b0.z = fmaf(ln_nm, s0.z, b0.z); b0.w = fmaf(ln_nm, s0.w, b0.w);
+                            b1.x = fmaf(ln_nm, s1.x, b1.x); b1.y = fmaf(ln_nm, s1.y, b1.y);
+                            b1.z = fmaf(ln_nm, s1.z, b1.z); b1.w = fmaf(ln_nm, s1.w, b1.w);
+                            v[0] = fmaf(__uint_as_float(src[0]), ln_rs, b0.x); v[1] = fmaf(__uint_as_float(src[1]), ln_rs, b0.y);
+                            v[2] = fmaf(__uint_as_float(src[2]), ln_rs, b0.z); v[3] = fmaf(__uint_as_float(src[3]), ln_rs, b0.w);
+                            v[4] = fmaf(__uint_as_float(src[4]), ln_rs, b1.x); v[5] = fmaf(__uint_as_float(src[5]), ln_rs, b1.y);
+                            v[6] = fmaf(__uint_as_float(src[6]), ln_rs, b1.z); v[7] = fmaf(__uint_as_float(src[7]), ln_rs, b1.w);
+                        } else {
+                            v[0] = __uint_as_float(src[0]) + b0.x; v[1] = __uint_as_float(src[1]) + b0.y;
+                            v[2] = __uint_as_float(src[2]) + b0.z; v[3] = __uint_as_float(src[3]) + b0.w;
+                            v[4] = __uint_as_float(src[4]) + b1.x; v[5] = __uint_as_float(src[5]) + b1.y;
+                            v[6] = __uint_as_float(src[6]) + b1.z; v[7] = __uint_as_float(src[7]) + b1.w;
+                        }
+                        const float2 y0 = gelu_fast2(make_float2(v[0], v[1]));
+                        const float2 y1 = gelu_fast2(make_float2(v[2], v[3]));
+                        const float2 y2 = gelu_fast2(make_float2(v[4], v[5]));
+                        const float2 y3 = gelu_fast2(make_float2(v[6], v[7]));
                         ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
                                     make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
                     }

@@ -91,6 +91,20 @@ def dwconv7_ln(x, w49, b, ln_w, ln_b, out_hi, out_lo=None, eps=1e-6, plan=None):
               B, H, W, Cc, eps, _stream())
 
 
+def dwconv7_stats(x, w49, b, out, stats, plan=None):
+    """x [B,H,W,C] fp32 -> out [B*H*W, C] bf16 (conv + bias, not normalised), stats [B*H*W, C/32, 2] fp32."""
+    _need_cuda(x, w49, b, out, stats)
+    B, H, W, Cc = x.shape
+    _lib.call("cpn_dwconv7_stats", _ph(plan), ptr(x), ptr(w49), ptr(b), ptr(out), ptr(stats), B, H, W, Cc, _stream())
+
+
+def gemm_ln_gelu(a, bw, M, N, K, stats, nparts, colsum, bias, out_bf16, eps=1e-6, plan=None):
+    """out = gelu(LayerNorm-folded fc1): see cpn_gemm_ln_gelu in include/cpn_b200.h."""
+    _need_cuda(a, bw, stats, colsum, bias, out_bf16)
+    _lib.call("cpn_gemm_ln_gelu", _ph(plan), ptr(a), ptr(bw), M, N, K, ptr(stats), nparts, ptr(colsum), ptr(bias),
+              float(eps), ptr(out_bf16), _stream())
+
+
 def ln_im2col2(x, ln_w, ln_b, out_hi, out_lo=None, stride=2, eps=1e-6, plan=None):
     """x [B,H,W,C] fp32 -> out [B*Ho*Wo, 4C] bf16."""
     _need_cuda(x, ln_w, ln_b, out_hi, out_lo)

@@ -82,6 +82,14 @@ class ConvNeXtProgram:
                     c = dw.out_channels
                     d["w49"] = dw.weight.detach().reshape(c, 49).t().contiguous()
                     d["w1"], d["w1_lo"] = _split(fc1.weight.detach(), split)
+                    if not split and c in (96, 192, 384, 768):
+                        # bf16 mode: LayerNorm folded into fc1 (csrc/gemm_tma_epi.cuh, EPI_LN_GELU_BF16):
+                        #   fc1(LN(y)) = rstd * (y @ (W1*gamma)^T - mean * rowsum(W1*gamma)) + (b1 + W1 @ beta)
+                        ln = blk.block[2]
+                        w1 = fc1.weight.detach().float()
+                        d["w1g"] = (w1 * ln.weight.detach().float()[None, :]).to(torch.bfloat16).contiguous()
+                        d["w1g_sum"] = d["w1g"].float().sum(1).contiguous()
+                        d["b1f"] = (fc1.bias.detach().float() + w1 @ ln.bias.detach().float()).contiguous()
                     d["w2"], d["w2_lo"] = _split(fc2.weight.detach(), split)
                 elif s[0] == "down":
                     conv = s[2]
@@ -110,10 +118,16 @@ class ConvNeXtProgram:
                 T = B * H * W
                 a_hi, a_lo = em.pair("act", (T, C))
                 h_hi, h_lo = em.pair("hid", (T, 4 * C))
-                ops.dwconv7_ln(res, pk["w49"], dw.bias.detach(), ln.weight.detach(), ln.bias.detach(), a_hi, a_lo,
-                               eps=ln.eps, plan=plan)
-                ops.gemm_bf16(a_hi, pk["w1"], T, 4 * C, C, a_lo=a_lo, bw_lo=pk["w1_lo"], bias=fc1.bias.detach(),
-                              out_bf16=h_hi, out_bf16_lo=h_lo, act=_lib.ACT_GELU, plan=plan)
+                if "w1g" in pk:
+                    stats = em.buf("ln_stats", (T, C // 32, 2), torch.float32)
+                    ops.dwconv7_stats(res, pk["w49"], dw.bias.detach(), a_hi, stats, plan=plan)
+                    ops.gemm_ln_gelu(a_hi, pk["w1g"], T, 4 * C, C, stats, C // 32, pk["w1g_sum"], pk["b1f"], h_hi,
+                                     eps=ln.eps, plan=plan)
+                else:
+                    ops.dwconv7_ln(res, pk["w49"], dw.bias.detach(), ln.weight.detach(), ln.bias.detach(), a_hi, a_lo,
+                                   eps=ln.eps, plan=plan)
+                    ops.gemm_bf16(a_hi, pk["w1"], T, 4 * C, C, a_lo=a_lo, bw_lo=pk["w1_lo"], bias=fc1.bias.detach(),
+                                  out_bf16=h_hi, out_bf16_lo=h_lo, act=_lib.ACT_GELU, plan=plan)
                 ops.gemm_bf16(h_hi, pk["w2"], T, C, 4 * C, a_lo=h_lo, bw_lo=pk["w2_lo"], bias=fc2.bias.detach(),
                               scale=blk.layer_scale.detach().view(C), res_f32=res, out_f32=res, plan=plan)
             else:

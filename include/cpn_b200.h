@@ -72,6 +72,19 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
                    const float* ln_b, void* out_hi, void* out_lo, int B, int H, int W, int C, float eps,
                    void* stream);
 
+/* bf16-mode split of the same CNBlock head (torchvision/models/convnext.py:52-55): the depthwise conv writes the
+ * UN-normalised result and per-token partial LayerNorm sums, and the LayerNorm is folded into the fc1 GEMM.
+ * cpn_dwconv7_stats: x [B,H,W,C] fp32, w49 [49,C], bias [C]  ->  out [B*H*W, C] bf16 = round(conv + bias),
+ *   stats [B*H*W, C/32, 2] fp32 = (sum, sum of squares) of the rounded values over each 32-channel group.
+ *   C must be 96, 192, 384 or 768.
+ * cpn_gemm_ln_gelu: out[M,N] bf16 = gelu(rstd_m * (A[M,K] * Bw[N,K]^T - mean_m * colsum[n]) + bias[n]) with
+ *   Bw = bf16(W1 * ln_weight), colsum[n] = sum_k Bw[n,k], bias = b1 + W1 * ln_bias, and mean_m / rstd_m rebuilt from
+ *   stats [M, nparts, 2] (K = C channels per token) -- equals gelu(fc1(LayerNorm(A))) of convnext.py:53-56. */
+int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
+                      float* stats, int B, int H, int W, int C, void* stream);
+int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N, int K, const float* stats,
+                     int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream);
+
 /* LayerNorm2d(C) then the im2col rows of Conv2d(C,C',k=2,stride) -- torchvision/models/convnext.py:146-150 with
  * the stride surgery of features/convnext_features.py:5-15.
  * x [B,H,W,C] fp32; out [B*Ho*Wo, 4*C] bf16 with column (kh*2+kw)*C + c, Ho = (H-2)/stride+1. */

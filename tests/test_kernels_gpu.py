@@ -127,6 +127,55 @@ def test_dwconv7_ln(cuda_device, B, H, W, C):
     assert ((out.float() + lo.float()) - ref).abs().max().item() < 5e-4
 
 
+@pytest.mark.parametrize("B,H,W,C", [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192),
+                                     (1, 56, 56, 96), (2, 3, 2, 96), (1, 1, 1, 384), (1, 54, 54, 768)])
+def test_dwconv7_stats(cuda_device, B, H, W, C):
+    """Un-normalised depthwise conv (bf16) + per-32-channel partial LayerNorm sums, vs F.conv2d in fp32."""
+    g = torch.Generator().manual_seed(C + H)
+    x = torch.randn(B, H, W, C, generator=g).to(cuda_device)
+    w = (torch.randn(C, 1, 7, 7, generator=g) * 0.2).to(cuda_device)
+    b = torch.randn(C, generator=g).to(cuda_device)
+    T = B * H * W
+    out = torch.full((T, C), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    stats = torch.full((T, C // 32, 2), float("nan"), device=cuda_device)
+    w49 = w.reshape(C, 49).t().contiguous()
+    ops.dwconv7_stats(x, w49, b, out, stats)
+    out2, stats2 = torch.empty_like(out), torch.empty_like(stats)
+    ops.dwconv7_stats(x, w49, b, out2, stats2)
+    torch.backends.cudnn.allow_tf32 = False
+    ref = F.conv2d(x.permute(0, 3, 1, 2), w, b, padding=3, groups=C).permute(0, 2, 3, 1).reshape(T, C)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2) and torch.equal(stats, stats2)  # fixed summation order
+    assert (out.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 1e-5
+    # the sums are those of the ROUNDED values, per 32-channel group
+    o = out.float().reshape(T, C // 32, 32)
+    assert torch.allclose(stats[..., 0], o.sum(-1), rtol=1e-5, atol=1e-4)
+    assert torch.allclose(stats[..., 1], (o * o).sum(-1), rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (1300, 768), (128, 96)])
+def test_gemm_ln_gelu(cuda_device, M, C):
+    """LayerNorm folded into fc1: gelu(fc1(LN(a))) from the un-normalised a and its partial sums."""
+    g = torch.Generator().manual_seed(C)
+    N = 4 * C
+    a = (torch.randn(M, C, generator=g) * 1.5 + 0.7).to(cuda_device).to(torch.bfloat16)
+    w1 = (torch.randn(N, C, generator=g) / C ** 0.5).to(cuda_device)
+    b1 = torch.randn(N, generator=g).to(cuda_device)
+    gamma = (torch.rand(C, generator=g) + 0.5).to(cuda_device)
+    beta = torch.randn(C, generator=g).to(cuda_device)
+    af = a.float().reshape(M, C // 32, 32)
+    stats = torch.stack([af.sum(-1), (af * af).sum(-1)], dim=-1).contiguous()
+    w1g = (w1 * gamma[None, :]).to(torch.bfloat16).contiguous()
+    colsum = w1g.float().sum(1).contiguous()
+    b1f = (b1 + w1 @ beta).contiguous()
+    out = torch.empty(M, N, device=cuda_device, dtype=torch.bfloat16)
+    ops.gemm_ln_gelu(a, w1g, M, N, C, stats, C // 32, colsum, b1f, out)
+    ref = F.gelu(F.linear(F.layer_norm(a.float(), (C,), gamma, beta, 1e-6), w1, b1))
+    torch.cuda.synchronize()
+    err = (out.float() - ref).abs().max().item()
+    assert err < 0.05 * max(1.0, ref.abs().max().item()) * 0.5, err
+
+
 @pytest.mark.parametrize("stride,H,W,C", [(2, 16, 16, 96), (1, 14, 14, 192), (1, 9, 11, 384)])
 def test_ln_im2col2(cuda_device, stride, H, W, C):
     g = torch.Generator().manual_seed(C)
