@@ -382,8 +382,8 @@ int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, d
 namespace {
 template <int C>
 int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
-               int nstrips, int rows, dim3 grid, cudaStream_t st) {
-    cpn::dwconv7_stats_kernel<C, 4><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+               int nstrips, int rows, int pf, dim3 grid, cudaStream_t st) {
+    cpn::dwconv7_stats_kernel<C><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows, pf);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -536,11 +536,14 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
         return fail("cpn_dwconv7_stats: C=%d is not a ConvNeXt-tiny width (96, 192, 384, 768)", C);
     if (B <= 0 || B > 65535 || H <= 0 || W <= 0) return fail("cpn_dwconv7_stats: bad shape B=%d H=%d W=%d", B, H, W);
     const int nstrips = (W + 3) / 4;
-    const int units = nstrips * (C / 32);
-    const int gx = (units + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
+    const int warps = (nstrips * (C / 32) + 1) / 2;  // a warp = two (strip, 32-channel group) units
+    const int gx = (warps + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
     // row segments: enough CTAs for >= 4 waves of 4 CTAs per SM, but segments no shorter than 7 rows
     int nseg = 1;
     while (static_cast<long long>(gx) * nseg * B < 16LL * num_sms() && (H + nseg) / (nseg + 1) >= 7) ++nseg;
+    if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knobs (tools/run_op.py)
+    int pf = cpn::DWS_PF;
+    if (const char* e = getenv("CPN_DWS_PF")) pf = atoi(e);
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;
     const dim3 grid(gx, nseg, B);
@@ -550,10 +553,10 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
              B, H, W, C, rows);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         switch (C) {
-            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
+            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
+            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
+            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
         }
     });
 }
@@ -562,6 +565,7 @@ int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N
                      int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream) {
     if (M <= 0 || N <= 0 || K <= 0) return fail("cpn_gemm_ln_gelu: bad shape M=%d N=%d K=%d", M, N, K);
     if (K % 8 != 0) return fail("cpn_gemm_ln_gelu: K must be a multiple of 8, K=%d", K);
+    if (nparts > cpn::LN_MAX_PARTS) return fail("cpn_gemm_ln_gelu: nparts=%d exceeds %d", nparts, cpn::LN_MAX_PARTS);
     if (nparts <= 0 || stats == nullptr || colsum == nullptr || bias == nullptr || out_bf16 == nullptr)
         return fail("cpn_gemm_ln_gelu: missing operand");
     const int epi = cpn::EPI_LN_GELU_BF16;

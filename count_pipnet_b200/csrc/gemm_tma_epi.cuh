@@ -24,6 +24,8 @@ namespace cpn {
 enum GemmEpi : int { EPI_GELU_BF16 = 0, EPI_SCALE_RES_F32 = 1, EPI_BIAS_F32 = 2, EPI_LN_GELU_BF16 = 3 };
 __host__ __device__ constexpr bool epi_out_bf16(int epi) { return epi == EPI_GELU_BF16 || epi == EPI_LN_GELU_BF16; }
 
+constexpr int LN_MAX_PARTS = 24;  // K = C <= 768 channels in 32-channel groups
+
 struct Gemm2Params {
     int M, N, K;
     int num_m_blocks, num_n_blocks, num_k_blocks;
@@ -183,17 +185,23 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             if (EPI == EPI_LN_GELU_BF16) {
                 const int row = min(row0 + lane, p.M - 1);
                 const float2* sp = reinterpret_cast<const float2*>(p.stats) + static_cast<size_t>(row) * p.nparts;
+                // all partial sums in flight at once (the row is read once per tile), then a fixed-order sum
+                float2 part[LN_MAX_PARTS];
+#pragma unroll
+                for (int i = 0; i < LN_MAX_PARTS; ++i)
+                    part[i] = i < p.nparts ? __ldg(sp + i) : make_float2(0.f, 0.f);
                 float s1 = 0.f, s2 = 0.f;
-                for (int i = 0; i < p.nparts; ++i) {
-                    const float2 v = __ldg(sp + i);
-                    s1 += v.x;
-                    s2 += v.y;
+#pragma unroll
+                for (int i = 0; i < LN_MAX_PARTS; ++i) {
+                    s1 += part[i].x;
+                    s2 += part[i].y;
                 }
                 const float mean = s1 * p.inv_k;
                 const float var = fmaxf(s2 * p.inv_k - mean * mean, 0.f);
                 ln_rs = rsqrtf(var + p.eps);
                 ln_nm = -mean * ln_rs;
             }
+            const float2 ln_rs2 = make_float2(ln_rs, ln_rs), ln_nm2 = make_float2(ln_nm, ln_nm);
             ptx::mbar_wait(&tmem_full_bar[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -232,30 +240,30 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const uint32_t* src = (j < 4) ? (r0 + 8 * j) : (r1 + 8 * (j - 4));
-                        float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
-                        float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
-                        float v[8];
+                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
+                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
+                        float2 v0 = make_float2(__uint_as_float(src[0]), __uint_as_float(src[1]));
+                        float2 v1 = make_float2(__uint_as_float(src[2]), __uint_as_float(src[3]));
+                        float2 v2 = make_float2(__uint_as_float(src[4]), __uint_as_float(src[5]));
+                        float2 v3 = make_float2(__uint_as_float(src[6]), __uint_as_float(src[7]));
                         if (EPI == EPI_LN_GELU_BF16) {
+                            // rstd * acc + (-mean * rstd * colsum + bias), two columns per instruction
                             const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j));
                             const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j + 4));
-                            b0.x = fmaf(ln_nm, s0.x, b0.x); b0.y = fmaf(ln_nm, s0.y, b0.y);
-                            b0.z = fmaf(ln_nm, s0.z, b0.z); b0.w = fmaf(ln_nm, s0.w, b0.w);
-                            b1.x = fmaf(ln_nm, s1.x, b1.x); b1.y = fmaf(ln_nm, s1.y, b1.y);
-                            b1.z = fmaf(ln_nm, s1.z, b1.z); b1.w = fmaf(ln_nm, s1.w, b1.w);
-                            v[0] = fmaf(__uint_as_float(src[0]), ln_rs, b0.x); v[1] = fmaf(__uint_as_float(src[1]), ln_rs, b0.y);
-                            v[2] = fmaf(__uint_as_float(src[2]), ln_rs, b0.z); v[3] = fmaf(__uint_as_float(src[3]), ln_rs, b0.w);
-                            v[4] = fmaf(__uint_as_float(src[4]), ln_rs, b1.x); v[5] = fmaf(__uint_as_float(src[5]), ln_rs, b1.y);
-                            v[6] = fmaf(__uint_as_float(src[6]), ln_rs, b1.z); v[7] = fmaf(__uint_as_float(src[7]), ln_rs, b1.w);
+                            v0 = ffma2(v0, ln_rs2, ffma2(ln_nm2, make_float2(s0.x, s0.y), make_float2(b0.x, b0.y)));
+                            v1 = ffma2(v1, ln_rs2, ffma2(ln_nm2, make_float2(s0.z, s0.w), make_float2(b0.z, b0.w)));
+                            v2 = ffma2(v2, ln_rs2, ffma2(ln_nm2, make_float2(s1.x, s1.y), make_float2(b1.x, b1.y)));
+                            v3 = ffma2(v3, ln_rs2, ffma2(ln_nm2, make_float2(s1.z, s1.w), make_float2(b1.z, b1.w)));
                         } else {
-                            v[0] = __uint_as_float(src[0]) + b0.x; v[1] = __uint_as_float(src[1]) + b0.y;
-                            v[2] = __uint_as_float(src[2]) + b0.z; v[3] = __uint_as_float(src[3]) + b0.w;
-                            v[4] = __uint_as_float(src[4]) + b1.x; v[5] = __uint_as_float(src[5]) + b1.y;
-                            v[6] = __uint_as_float(src[6]) + b1.z; v[7] = __uint_as_float(src[7]) + b1.w;
+                            v0 = fadd2(v0, make_float2(b0.x, b0.y));
+                            v1 = fadd2(v1, make_float2(b0.z, b0.w));
+                            v2 = fadd2(v2, make_float2(b1.x, b1.y));
+                            v3 = fadd2(v3, make_float2(b1.z, b1.w));
                         }
-                        const float2 y0 = gelu_fast2(make_float2(v[0], v[1]));
-                        const float2 y1 = gelu_fast2(make_float2(v[2], v[3]));
-                        const float2 y2 = gelu_fast2(make_float2(v[4], v[5]));
-                        const float2 y3 = gelu_fast2(make_float2(v[6], v[7]));
+                        const float2 y0 = gelu_sat2(v0);
+                        const float2 y1 = gelu_sat2(v1);
+                        const float2 y2 = gelu_sat2(v2);
+                        const float2 y3 = gelu_sat2(v3);
                         ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
                                     make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
                     }

@@ -29,6 +29,26 @@ def main():
         fn = lambda: ops.dwconv7_ln(x, w49, b, lw, lb, out)
         nbytes = x.numel() * 4 + out.numel() * 2
         flops = 2.0 * 49 * x.numel()
+    elif a.op == "dwstats":
+        x = torch.randn(a.B, a.H, a.W, a.C, generator=g).to(dev)
+        w49 = (torch.randn(49, a.C, generator=g) * 0.2).to(dev)
+        b = torch.randn(a.C, generator=g).to(dev)
+        out = torch.empty(a.B * a.H * a.W, a.C, device=dev, dtype=torch.bfloat16)
+        stats = torch.empty(a.B * a.H * a.W, a.C // 32, 2, device=dev)
+        fn = lambda: ops.dwconv7_stats(x, w49, b, out, stats)
+        nbytes = x.numel() * 4 + out.numel() * 2 + stats.numel() * 4
+        flops = 2.0 * 49 * x.numel()
+    elif a.op == "gemm_ln":
+        A = torch.randn(a.M, a.K, generator=g).to(dev).to(torch.bfloat16)
+        Wt = (torch.randn(a.N, a.K, generator=g) / a.K ** 0.5).to(dev).to(torch.bfloat16)
+        bias = torch.randn(a.N, generator=g).to(dev)
+        colsum = Wt.float().sum(1).contiguous()
+        af = A.float().reshape(a.M, a.K // 32, 32)
+        stats = torch.stack([af.sum(-1), (af * af).sum(-1)], dim=-1).contiguous()
+        out = torch.empty(a.M, a.N, device=dev, dtype=torch.bfloat16)
+        fn = lambda: ops.gemm_ln_gelu(A, Wt, a.M, a.N, a.K, stats, a.K // 32, colsum, bias, out)
+        nbytes = A.numel() * 2 + Wt.numel() * 2 + out.numel() * 2
+        flops = 2.0 * a.M * a.N * a.K
     elif a.op == "gemm":
         A = torch.randn(a.M, a.K, generator=g).to(dev).to(torch.bfloat16)
         Wt = (torch.randn(a.N, a.K, generator=g) / a.K ** 0.5).to(dev).to(torch.bfloat16)
