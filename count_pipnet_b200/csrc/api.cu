@@ -382,8 +382,8 @@ int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, d
 namespace {
 template <int C>
 int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
-               int nstrips, int rows, int pf, dim3 grid, cudaStream_t st) {
-    cpn::dwconv7_stats_kernel<C><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows, pf);
+               int nstrips, int rows, dim3 grid, cudaStream_t st) {
+    cpn::dwconv7_stats_kernel<C><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -538,12 +538,11 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
     const int nstrips = (W + 3) / 4;
     const int warps = (nstrips * (C / 32) + 1) / 2;  // a warp = two (strip, 32-channel group) units
     const int gx = (warps + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
-    // row segments: enough CTAs for >= 4 waves of 4 CTAs per SM, but segments no shorter than 7 rows
+    // row segments: every segment pays 6 halo rows of loads AND of FMAs (the body is branch-free), so split H only
+    // when the grid would not give each SM its two resident CTAs a few times over
     int nseg = 1;
-    while (static_cast<long long>(gx) * nseg * B < 16LL * num_sms() && (H + nseg) / (nseg + 1) >= 7) ++nseg;
+    while (static_cast<long long>(gx) * nseg * B < 6LL * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
     if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knobs (tools/run_op.py)
-    int pf = cpn::DWS_PF;
-    if (const char* e = getenv("CPN_DWS_PF")) pf = atoi(e);
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;
     const dim3 grid(gx, nseg, B);
@@ -553,10 +552,10 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
              B, H, W, C, rows);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         switch (C) {
-            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
-            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
-            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
-            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, pf, grid, st);
+            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
         }
     });
 }
@@ -602,6 +601,24 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
     set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2),
              "B=%d H=%d W=%d C=%d s=%d", B, H, W, C, stride);
+    if (lo == nullptr && C % 4 == 0 && C <= 768) {
+        // bf16 mode: vectorised persistent kernel, two tokens in flight per warp
+        const int nv = (C / 4 + 31) / 32;
+        long long want = (ntok + 15) / 16;
+        const long long cap = 8LL * num_sms();
+        const int pgrid = static_cast<int>(want < cap ? want : cap);
+        return submit(plan, stream, [=](cudaStream_t st) -> int {
+            switch (nv) {
+                case 1: cpn::ln_im2col2_bf16_kernel<1><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;
+                case 2: cpn::ln_im2col2_bf16_kernel<2><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;
+                case 3: cpn::ln_im2col2_bf16_kernel<3><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;
+                case 4: cpn::ln_im2col2_bf16_kernel<4><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;
+                default: cpn::ln_im2col2_bf16_kernel<6><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;
+            }
+            CPN_CUDA(cudaGetLastError());
+            return 0;
+        });
+    }
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::ln_im2col2_kernel<<<grid, 256, 0, st>>>(x, ln_w, ln_b, hi, lo, B, H, W, C, stride, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());
@@ -720,6 +737,24 @@ int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float 
     if (smem > 200 * 1024) return fail("cpn_softmax_pool: P=%d too large", P);
     const dim3 grid(chunks, B);
     set_info("softmax_pool", 4.0 * B * HW * P, 4.0 * B * HW * P * (1 + (gumbel != nullptr) + (map != nullptr)));
+    if (gumbel == nullptr && !hard && map == nullptr && P % 128 == 0 && P <= 1024) {
+        // plain softmax, map not requested: register-resident kernel (smem <= 32 KB)
+        const int nv = P / 128;
+        return submit(plan, stream, [=](cudaStream_t st) -> int {
+            switch (nv) {
+                case 1: cpn::softmax_pool_reg_kernel<1><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 2: cpn::softmax_pool_reg_kernel<2><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 3: cpn::softmax_pool_reg_kernel<3><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 4: cpn::softmax_pool_reg_kernel<4><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 5: cpn::softmax_pool_reg_kernel<5><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 6: cpn::softmax_pool_reg_kernel<6><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                case 7: cpn::softmax_pool_reg_kernel<7><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                default: cpn::softmax_pool_reg_kernel<8><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+            }
+            CPN_CUDA(cudaGetLastError());
+            return 0;
+        });
+    }
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -30,9 +30,11 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
     return *reinterpret_cast<float2*>(&rd);
 }
 
+// bf16(a) in the low half, bf16(b) in the high half (round to nearest even): one F2FP instead of two F2F + shift/or.
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-    return static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(a))) |
-           (static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(b))) << 16);
+    uint32_t d;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+    return d;
 }
 __device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 
@@ -284,6 +286,79 @@ ln_im2col2_kernel(const float* __restrict__ x, const float* __restrict__ ln_w, c
                 const __nv_bfloat16 hv = __float2bfloat16_rn(v[i]);
                 out_hi[o + lane + 32 * i] = hv;
                 if (out_lo != nullptr) out_lo[o + lane + 32 * i] = __float2bfloat16_rn(v[i] - __bfloat162float(hv));
+            }
+        }
+    }
+}
+
+// bf16-only variant (no lo plane), NV = ceil(C / 128) float4 per lane: a lane owns 4 consecutive channels per chunk,
+// so a token row is read with 16-byte loads (512 B per warp and instruction) and each of its im2col copies is written
+// with 8-byte stores; two tokens are in flight per warp and warps stride over the token list (persistent grid).
+template <int NV>
+__global__ void __launch_bounds__(256)
+ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                       __nv_bfloat16* __restrict__ out, int B, int H, int W, int C, int stride, int Ho, int Wo,
+                       float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long ntok = static_cast<long long>(B) * H * W;
+    const long long nwarps = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
+    const int nchunk = C >> 2;  // float4 chunks per token
+    float4 gw[NV], gb[NV];
+    bool act[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        act[i] = lane + 32 * i < nchunk;
+        gw[i] = act[i] ? __ldg(reinterpret_cast<const float4*>(ln_w) + lane + 32 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        gb[i] = act[i] ? __ldg(reinterpret_cast<const float4*>(ln_b) + lane + 32 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float inv_c = 1.0f / static_cast<float>(C);
+    for (long long t = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp) * 2; t < ntok; t += 2 * nwarps) {
+        const int ntk = t + 1 < ntok ? 2 : 1;
+        float4 v[2][NV];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const float4* xr = reinterpret_cast<const float4*>(x + (t + (u < ntk ? u : 0)) * C);
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[u][i] = act[i] ? __ldg(xr + lane + 32 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (u >= ntk) break;
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) s += (v[u][i].x + v[u][i].y) + (v[u][i].z + v[u][i].w);
+            const float mean = warp_sum(s) * inv_c;
+            float ss = 0.f;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                if (act[i]) {
+                    v[u][i].x -= mean; v[u][i].y -= mean; v[u][i].z -= mean; v[u][i].w -= mean;
+                    ss += (v[u][i].x * v[u][i].x + v[u][i].y * v[u][i].y) + (v[u][i].z * v[u][i].z + v[u][i].w * v[u][i].w);
+                }
+            }
+            const float rstd = rsqrtf(warp_sum(ss) * inv_c + eps);
+            uint2 pk[NV];
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                pk[i].x = pack_bf16x2(fmaf(v[u][i].x * rstd, gw[i].x, gb[i].x), fmaf(v[u][i].y * rstd, gw[i].y, gb[i].y));
+                pk[i].y = pack_bf16x2(fmaf(v[u][i].z * rstd, gw[i].z, gb[i].z), fmaf(v[u][i].w * rstd, gw[i].w, gb[i].w));
+            }
+            const long long tok = t + u;
+            const int w = static_cast<int>(tok % W);
+            const int h = static_cast<int>((tok / W) % H);
+            const int b = static_cast<int>(tok / (static_cast<long long>(W) * H));
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const int kh = kk >> 1, kw = kk & 1;
+                const int hh = h - kh, ww = w - kw;
+                if (hh < 0 || ww < 0 || (hh % stride) != 0 || (ww % stride) != 0) continue;
+                const int ho = hh / stride, wo = ww / stride;
+                if (ho >= Ho || wo >= Wo) continue;
+                uint2* o = reinterpret_cast<uint2*>(out + ((static_cast<size_t>(b) * Ho + ho) * Wo + wo) * (4 * static_cast<size_t>(C)) +
+                                                    static_cast<size_t>(kk) * C);
+#pragma unroll
+                for (int i = 0; i < NV; ++i)
+                    if (act[i]) o[lane + 32 * i] = pk[i];
             }
         }
     }

@@ -103,6 +103,89 @@ softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbe
     }
 }
 
+// Register-resident variant for the common case (plain softmax, no map, P a multiple of 128 up to 1024): each lane
+// owns the same 4*NV prototypes of every token (NV float4 per lane, loaded once, coalesced 512 B per warp and
+// instruction), so the row max / sum are two warp reductions, the probabilities never leave registers and the running
+// spatial max / sum stays in registers too; two tokens are in flight per warp. Same grid and partial layout as above.
+// exp() is ex2.approx of a pre-scaled argument: relative error 2^-22, well inside the fp32-mode parity bar (1e-4).
+template <int NV>
+__global__ void __launch_bounds__(256)
+softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict__ partial, int HW, int chunks) {
+    constexpr int P = NV * 128;
+    extern __shared__ float s_pool[];  // [warps][P]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const int b = blockIdx.y;
+    const int chunk = blockIdx.x;
+    const int per_chunk = (HW + chunks - 1) / chunks;
+    const int t0 = chunk * per_chunk;
+    const int t1 = min(HW, t0 + per_chunk);
+    constexpr float LOG2E = 1.4426950408889634f;
+    float4 pool[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) pool[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // probabilities are >= 0
+    const float4* zb = reinterpret_cast<const float4*>(z + static_cast<size_t>(b) * HW * P) + lane;
+    for (int t = t0 + 2 * warp; t < t1; t += 2 * wpb) {
+        const bool two = t + 1 < t1;
+        float4 v[2][NV];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const float4* zr = zb + static_cast<size_t>(u == 1 && two ? t + 1 : t) * (P / 4);
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[u][i] = __ldg(zr + 32 * i);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            float m = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) m = fmaxf(fmaxf(fmaxf(v[u][i].x, v[u][i].y), fmaxf(v[u][i].z, v[u][i].w)), m);
+            m = warp_max(m);
+            const float ms = m * LOG2E;
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                v[u][i].x = exp2f(fmaf(v[u][i].x, LOG2E, -ms));
+                v[u][i].y = exp2f(fmaf(v[u][i].y, LOG2E, -ms));
+                v[u][i].z = exp2f(fmaf(v[u][i].z, LOG2E, -ms));
+                v[u][i].w = exp2f(fmaf(v[u][i].w, LOG2E, -ms));
+                s += (v[u][i].x + v[u][i].y) + (v[u][i].z + v[u][i].w);
+            }
+            s = warp_sum(s);
+            const float inv_s = (u == 1 && !two) ? 0.f : 1.0f / s;  // the duplicate of an odd tail contributes nothing
+            if (mode == POOL_MAX) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    pool[i].x = fmaxf(pool[i].x, v[u][i].x * inv_s);
+                    pool[i].y = fmaxf(pool[i].y, v[u][i].y * inv_s);
+                    pool[i].z = fmaxf(pool[i].z, v[u][i].z * inv_s);
+                    pool[i].w = fmaxf(pool[i].w, v[u][i].w * inv_s);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    pool[i].x = fmaf(v[u][i].x, inv_s, pool[i].x);
+                    pool[i].y = fmaf(v[u][i].y, inv_s, pool[i].y);
+                    pool[i].z = fmaf(v[u][i].z, inv_s, pool[i].z);
+                    pool[i].w = fmaf(v[u][i].w, inv_s, pool[i].w);
+                }
+            }
+        }
+    }
+    float4* mine = reinterpret_cast<float4*>(s_pool + warp * P) + lane;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) mine[32 * i] = pool[i];
+    __syncthreads();
+    float* out = partial + (static_cast<size_t>(b) * chunks + chunk) * P;
+    for (int p = threadIdx.x; p < P; p += blockDim.x) {
+        float a = s_pool[p];
+        for (int wv = 1; wv < wpb; ++wv) {
+            const float o = s_pool[wv * P + p];
+            a = (mode == POOL_MAX) ? fmaxf(a, o) : a + o;
+        }
+        out[p] = a;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ tail
 enum Encoding : int { ENC_NONE = 0, ENC_ONEHOT = 1, ENC_LINEAR = 2, ENC_LINEAR_FULL = 3, ENC_BILINEAR = 4, ENC_IDENTITY = 5 };
 

@@ -214,6 +214,23 @@ def test_softmax_pool_and_map(cuda_device, mode, P):
         assert (partial.sum(1) - sm.sum(1)).abs().max().item() < 1e-4
 
 
+@pytest.mark.parametrize("mode", [_lib.POOL_MAX, _lib.POOL_SUM])
+@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5)])
+def test_softmax_pool_register_path(cuda_device, mode, P, HW, chunks):
+    """Plain softmax without the map (register-resident kernel), odd token counts and ragged chunks."""
+    g = torch.Generator().manual_seed(P + HW)
+    B = 3
+    z = (torch.randn(B, HW, P, generator=g) * 3).to(cuda_device)
+    partial = torch.full((B, chunks, P), float("nan"), device=cuda_device)
+    ops.softmax_pool(z, partial, B, HW, P, chunks, mode=mode)
+    sm = torch.softmax(z, dim=2)
+    torch.cuda.synchronize()
+    if mode == _lib.POOL_MAX:
+        assert (partial.amax(1) - sm.amax(1)).abs().max().item() < 1e-6
+    else:
+        assert (partial.sum(1) - sm.sum(1)).abs().max().item() < 1e-4
+
+
 def test_softmax_pool_gumbel_hard(cuda_device):
     g = torch.Generator().manual_seed(9)
     B, HW, P, chunks = 2, 64, 16, 2
