@@ -222,33 +222,59 @@ struct Gemm2Launch {
     CUtensorMap ta, tb, tout;
     cpn::Gemm2Params p;
     int grid;
+    int cg;  // 1: one CTA per 128-row tile; 2: CTA pairs (cta_group::2) on 256-row tiles
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, int CG>
 int launch_gemm2_inst(const Gemm2Launch& g, cudaStream_t st) {
-    using S = cpn::Gemm2Cfg<BN, EPI>;
-    auto kern = cpn::gemm_tma_epi_kernel<BN, EPI>;
+    using S = cpn::Gemm2Cfg<BN, EPI, CG>;
+    auto kern = cpn::gemm_tma_epi_kernel<BN, EPI, CG>;
     static bool attr_done = false;
     if (!attr_done) {
         CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         attr_done = true;
     }
-    kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
+    if (CG == 1) {
+        kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
+    } else {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(g.grid);
+        cfg.blockDim = dim3(cpn::GEMM_THREADS);
+        cfg.dynamicSmemBytes = S::TOTAL;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CPN_CUDA(cudaLaunchKernelEx(&cfg, kern, g.ta, g.tb, g.tout, g.p));
+    }
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
 
 template <int EPI>
 int launch_gemm2_bn(const Gemm2Launch& g, int bn, cudaStream_t st) {
+    if (g.cg == 2) {
+        switch (bn) {
+            case 256: return launch_gemm2_inst<256, EPI, 2>(g, st);
+            case 192: return launch_gemm2_inst<192, EPI, 2>(g, st);
+            case 128: return launch_gemm2_inst<128, EPI, 2>(g, st);
+        }
+        return fail("no CTA-pair GEMM instantiation for BN=%d", bn);
+    }
     switch (bn) {
-        case 256: return launch_gemm2_inst<256, EPI>(g, st);
-        case 192: return launch_gemm2_inst<192, EPI>(g, st);
-        case 128: return launch_gemm2_inst<128, EPI>(g, st);
-        case 64: return launch_gemm2_inst<64, EPI>(g, st);
+        case 256: return launch_gemm2_inst<256, EPI, 1>(g, st);
+        case 192: return launch_gemm2_inst<192, EPI, 1>(g, st);
+        case 128: return launch_gemm2_inst<128, EPI, 1>(g, st);
+        case 64: return launch_gemm2_inst<64, EPI, 1>(g, st);
     }
     if (!cpn::epi_out_bf16(EPI)) {
-        if (bn == 96) return launch_gemm2_inst<96, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI>(g, st);
-        if (bn == 32) return launch_gemm2_inst<32, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI>(g, st);
+        if (bn == 96) return launch_gemm2_inst<96, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI, 1>(g, st);
+        if (bn == 32) return launch_gemm2_inst<32, cpn::epi_out_bf16(EPI) ? cpn::EPI_BIAS_F32 : EPI, 1>(g, st);
     }
     return fail("no TMA-epilogue GEMM instantiation for BN=%d", bn);
 }
@@ -278,6 +304,30 @@ int pick_bn2(int M, int N, int epi) {
         if (N % bn == 0 && bn % chunk == 0 && bn >= 64) return bn;
     }
     return best;
+}
+
+int make_tmap(CUtensorMap* m, const void* ptr, long long rows, int K, int box_rows);
+
+// Tile geometry of a TMA-epilogue GEMM: CTA pairs (cta_group::2, 256-row tiles, each CTA stages half of the B tile)
+// when the tile is wide enough to split and there is at least one pair tile per SM pair; CPN_GEMM_2SM=0 disables.
+int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, int epi) {
+    static const int allow = [] { const char* e = getenv("CPN_GEMM_2SM"); return e == nullptr ? 1 : atoi(e); }();
+    const int pairs = num_sms() / 2;
+    const long long pair_tiles = static_cast<long long>((M + 2 * cpn::GEMM_BM - 1) / (2 * cpn::GEMM_BM)) * (N / bn);
+    // Measured (profiles/r01_gemm_pairs.md): pairs help the K-heavy fp32-output GEMMs (fc2: +4 % at K=1536, +14 % at
+    // K=3072) and cost a few percent on the epilogue-heavy bf16-output ones (fc1), so only the former use them.
+    const bool wanted = !cpn::epi_out_bf16(epi) || allow >= 2;  // CPN_GEMM_2SM=2 forces pairs everywhere (tests)
+    g.cg = (allow != 0 && wanted && (bn == 256 || bn == 192 || bn == 128) && (pair_tiles >= pairs || allow == 2)) ? 2 : 1;
+    if (make_tmap(&g.tb, Bw, N, K, bn / g.cg) != 0) return -1;
+    g.p.num_m_blocks = (M + g.cg * cpn::GEMM_BM - 1) / (g.cg * cpn::GEMM_BM);
+    g.p.num_n_blocks = N / bn;
+    g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+    static const int order = [] { const char* e = getenv("CPN_GEMM_ORDER"); return e == nullptr ? 0 : atoi(e); }();
+    g.p.m_fastest = order;
+    const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
+    const int slots = num_sms() / g.cg;
+    g.grid = g.cg * (tiles < slots ? tiles : slots);
+    return 0;
 }
 
 }  // namespace
@@ -573,19 +623,14 @@ int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N
     Gemm2Launch g;
     memset(&g, 0, sizeof(g));
     if (make_tmap(&g.ta, A, M, K, cpn::GEMM_BM) != 0) return -1;
-    if (make_tmap(&g.tb, Bw, N, K, bn2) != 0) return -1;
     if (make_tmap_out(&g.tout, out_bf16, M, N, true) != 0) return -1;
     g.p.M = M; g.p.N = N; g.p.K = K;
-    g.p.num_m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
-    g.p.num_n_blocks = N / bn2;
-    g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+    if (gemm2_geometry(g, Bw, M, N, K, bn2, epi) != 0) return -1;
     g.p.bias = bias; g.p.scale = nullptr;
     g.p.stats = stats; g.p.colsum = colsum; g.p.nparts = nparts; g.p.inv_k = 1.0f / static_cast<float>(K); g.p.eps = eps;
-    const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
-    g.grid = tiles < num_sms() ? tiles : num_sms();
     const double mn = static_cast<double>(M) * N;
     set_info("gemm_bf16", 2.0 * mn * K, 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) + 2.0 * mn,
-             "M=%d N=%d K=%d BN=%d epi=ln_gelu_bf16", M, N, K, bn2);
+             "M=%d N=%d K=%d BN=%d cg=%d epi=ln_gelu_bf16", M, N, K, bn2, g.cg);
     return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
 }
 
@@ -652,20 +697,15 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
             Gemm2Launch g;
             memset(&g, 0, sizeof(g));
             if (make_tmap(&g.ta, A, M, K, cpn::GEMM_BM) != 0) return -1;
-            if (make_tmap(&g.tb, Bw, N, K, bn2) != 0) return -1;
             const bool obf = epi == cpn::EPI_GELU_BF16;
             if (make_tmap_out(&g.tout, obf ? out_bf16 : static_cast<void*>(out_f32), M, N, obf) != 0) return -1;
             g.p.M = M; g.p.N = N; g.p.K = K;
-            g.p.num_m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
-            g.p.num_n_blocks = N / bn2;
-            g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
+            if (gemm2_geometry(g, Bw, M, N, K, bn2, epi) != 0) return -1;
             g.p.bias = bias; g.p.scale = scale;
-            const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
-            g.grid = tiles < num_sms() ? tiles : num_sms();
             const double mn = static_cast<double>(M) * N;
             const double bytes = 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) +
                                  (obf ? 2.0 : (epi == cpn::EPI_SCALE_RES_F32 ? 8.0 : 4.0)) * mn;
-            set_info("gemm_bf16", 2.0 * mn * K, bytes, "M=%d N=%d K=%d BN=%d epi=%s", M, N, K, bn2,
+            set_info("gemm_bf16", 2.0 * mn * K, bytes, "M=%d N=%d K=%d BN=%d cg=%d epi=%s", M, N, K, bn2, g.cg,
                      obf ? "gelu_bf16" : (epi == cpn::EPI_SCALE_RES_F32 ? "scale_res_f32" : "bias_f32"));
             return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
         }

@@ -37,12 +37,17 @@ struct Gemm2Params {
     int nparts;
     float inv_k;          // 1 / C
     float eps;
+    // tile order: 0 = consecutive tiles walk the N blocks of one M block (co-running CTAs share the A tile),
+    // 1 = consecutive tiles walk the M blocks of one N block (co-running CTAs share the B tile)
+    int m_fastest;
 };
 
-template <int BN, int EPI>
+// CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cluster of two, tcgen05 cta_group::2) per 256 x BN tile;
+// each CTA stages its own 128 rows of A and HALF of the B tile, so operand traffic from L2 per FLOP drops by a third.
+template <int BN, int EPI, int CG = 1>
 struct Gemm2Cfg {
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
-    static constexpr int B_BYTES = BN * GEMM_BK * 2;
+    static constexpr int B_BYTES = (BN / CG) * GEMM_BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int CHUNK_COLS = epi_out_bf16(EPI) ? 64 : 32;  // 128 bytes of output per row
     static constexpr int NCHUNK = BN / CHUNK_COLS;
@@ -59,13 +64,15 @@ struct Gemm2Cfg {
     static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, int CG = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_out, const Gemm2Params p) {
-    using S = Gemm2Cfg<BN, EPI>;
+    using S = Gemm2Cfg<BN, EPI, CG>;
     constexpr int STAGES = S::STAGES;
     static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N constraint for M=128");
+    static_assert(CG == 1 || (CG == 2 && BN % 32 == 0), "a CTA pair splits the B tile in two halves of BN/2 rows");
+    const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;  // rank 0 of a pair issues the MMAs
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -81,7 +88,8 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // m blocks are 128 * CG rows
+    const int tile0 = blockIdx.x / CG, tile_step = gridDim.x / CG;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmap_a);
@@ -93,16 +101,22 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(&tmem_full_bar[s], 1);
-            ptx::mbar_init(&tmem_empty_bar[s], GEMM_EPI_WARPS);
+            ptx::mbar_init(&tmem_empty_bar[s], CG * GEMM_EPI_WARPS);  // both CTAs' epilogues report to the leader
         }
         for (int s = 0; s < 2 * GEMM_EPI_WARPS; ++s) ptx::mbar_init(&res_bar[s], 1);
         ptx::fence_mbar_init();
     } else if (warp == 2) {
-        ptx::tmem_alloc(tmem_holder, S::TMEM_COLS);
-        ptx::tmem_relinquish();
+        if (CG == 2) {
+            ptx::tmem_alloc_2sm(tmem_holder, S::TMEM_COLS);
+            ptx::tmem_relinquish_2sm();
+        } else {
+            ptx::tmem_alloc(tmem_holder, S::TMEM_COLS);
+            ptx::tmem_relinquish();
+        }
     }
     ptx::tc_fence_before();
-    __syncthreads();
+    if (CG == 2) ptx::cluster_sync();  // the peer's barriers are initialised before anything arrives on them
+    else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
 
@@ -111,14 +125,23 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m_blk = tile / p.num_n_blocks;
-                const int n_blk = tile % p.num_n_blocks;
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+                const int m_blk = p.m_fastest ? tile % p.num_m_blocks : tile / p.num_n_blocks;
+                const int n_blk = p.m_fastest ? tile / p.num_m_blocks : tile % p.num_n_blocks;
+                const int m0 = (m_blk * CG + static_cast<int>(rank)) * GEMM_BM;
+                const int n0 = n_blk * BN + static_cast<int>(rank) * (BN / CG);
                 for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                    ptx::mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
-                    ptx::tma_load_2d(stage_a(stage), &tmap_a, kb * GEMM_BK, m_blk * GEMM_BM, &full_bar[stage]);
-                    ptx::tma_load_2d(stage_b(stage), &tmap_b, kb * GEMM_BK, n_blk * BN, &full_bar[stage]);
+                    if (CG == 2) {
+                        // both CTAs' bytes are counted on the leader's barrier, which the MMA thread waits on
+                        if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * S::STAGE_BYTES);
+                        ptx::tma_load_2d_2sm(stage_a(stage), &tmap_a, kb * GEMM_BK, m0, &full_bar[stage]);
+                        ptx::tma_load_2d_2sm(stage_b(stage), &tmap_b, kb * GEMM_BK, n0, &full_bar[stage]);
+                    } else {
+                        ptx::mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+                        ptx::tma_load_2d(stage_a(stage), &tmap_a, kb * GEMM_BK, m0, &full_bar[stage]);
+                        ptx::tma_load_2d(stage_b(stage), &tmap_b, kb * GEMM_BK, n0, &full_bar[stage]);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -126,12 +149,12 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         __syncwarp();
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer (single thread)
-        if (lane == 0) {
-            constexpr uint32_t idesc = ptx::make_idesc_bf16(GEMM_BM, BN);
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(GEMM_BM * CG, BN);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
@@ -143,10 +166,17 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     const uint64_t adesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_a(stage)));
                     const uint64_t bdesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_b(stage)));
 #pragma unroll
-                    for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k)
-                        ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    ptx::umma_commit(&empty_bar[stage]);
-                    if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[as]);
+                    for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k) {
+                        if (CG == 2) ptx::umma_bf16_2sm(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        else ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    }
+                    if (CG == 2) {
+                        ptx::umma_commit_2sm(&empty_bar[stage]);  // frees the stage in both CTAs
+                        if (kb == p.num_k_blocks - 1) ptx::umma_commit_2sm(&tmem_full_bar[as]);
+                    } else {
+                        ptx::umma_commit(&empty_bar[stage]);
+                        if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[as]);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -164,12 +194,12 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;  // this lane's row inside a staging block
         uint32_t g = 0;  // chunks processed so far by this warp: buffer = g & 1, barrier parity = (g >> 1) & 1
         int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int m_blk = tile / p.num_n_blocks;
-            const int n_blk = tile % p.num_n_blocks;
+        for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
+            const int m_blk = p.m_fastest ? tile % p.num_m_blocks : tile / p.num_n_blocks;
+            const int n_blk = p.m_fastest ? tile / p.num_m_blocks : tile % p.num_n_blocks;
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
-            const int row0 = m_blk * GEMM_BM + q * 32;
+            const int row0 = (m_blk * CG + static_cast<int>(rank)) * GEMM_BM + q * 32;
             const int col_tile = n_blk * BN;
             if (EPI == EPI_SCALE_RES_F32 && half < S::NCHUNK) {
                 // residual of the first chunk: does not depend on the accumulator, so it travels while the MMAs run
@@ -234,7 +264,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     if (last) {
                         ptx::tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+                        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_leader(&tmem_empty_bar[as]); else ptx::mbar_arrive(&tmem_empty_bar[as]); }
                     }
                     // 64 columns -> gelu(acc + bias) -> 8 x 16 bytes of bf16
 #pragma unroll
@@ -272,7 +302,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     if (last) {
                         ptx::tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+                        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_leader(&tmem_empty_bar[as]); else ptx::mbar_arrive(&tmem_empty_bar[as]); }
                     }
                     if (EPI == EPI_SCALE_RES_F32) ptx::mbar_wait(&rbar[b], (g >> 1) & 1);
                     // 32 columns -> res + scale * (acc + bias) (or acc + bias) -> 8 x 16 bytes of fp32
@@ -302,7 +332,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             if (half >= S::NCHUNK) {  // a tile narrower than two chunks leaves this warp without work
                 ptx::tc_fence_before();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[as]);
+                if (lane == 0) { if (CG == 2) ptx::mbar_arrive_leader(&tmem_empty_bar[as]); else ptx::mbar_arrive(&tmem_empty_bar[as]); }
             }
         }
         if (lane == 0) ptx::bulk_wait<0>();  // all stores complete before the CTA (and its shared memory) goes away
@@ -310,10 +340,12 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
 
     ptx::tc_fence_before();
-    __syncthreads();
+    if (CG == 2) ptx::cluster_sync();  // neither CTA's shared memory / TMEM goes away while the pair still uses it
+    else __syncthreads();
     if (warp == 2) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc(tmem_base, S::TMEM_COLS);
+        if (CG == 2) ptx::tmem_dealloc_2sm(tmem_base, S::TMEM_COLS);
+        else ptx::tmem_dealloc(tmem_base, S::TMEM_COLS);
     }
 }
 

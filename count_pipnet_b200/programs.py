@@ -5,6 +5,7 @@ bf16 (plus the bf16 "lo" planes in fp32 mode).
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -13,6 +14,12 @@ import torch.nn as nn
 from . import _lib, ops
 from .features import convnext_features as cnx
 from .features import resnet_features as rsn
+
+
+# Working-set target of one image chunk of a stage (bf16 mode); 0 = whole batch at once. Measured on B200 (B=64, cfg2):
+# chunking for L2 residency LOSES (6.6 ms at 96 MB chunks vs 4.9 ms unchunked) - the smaller GEMMs and depthwise convs
+# lose more to wave quantisation than the HBM round trips cost - so it is off unless CPN_L2_CHUNK_MB is set.
+L2_CHUNK_BYTES = float(os.environ.get("CPN_L2_CHUNK_MB", "0")) * 2 ** 20 or 1e18
 
 
 class Emit:
@@ -103,7 +110,10 @@ class ConvNeXtProgram:
         res = None
         C = 0
         n_res = 0
-        for s, pk in zip(self.steps, self.packed):
+        steps = list(zip(self.steps, self.packed))
+        i = 0
+        while i < len(steps):
+            s, pk = steps[i]
             if s[0] == "stem":
                 _, conv, ln = s
                 H, W = (H - 4) // 4 + 1, (W - 4) // 4 + 1
@@ -112,24 +122,13 @@ class ConvNeXtProgram:
                 n_res += 1
                 ops.stem_ln(x, conv.weight.detach().view(C, 48), conv.bias.detach(), ln.weight.detach(),
                             ln.bias.detach(), res, eps=ln.eps, plan=plan)
+                i += 1
             elif s[0] == "block":
-                blk = s[1]
-                dw, ln, fc1, fc2 = blk.block[0], blk.block[2], blk.block[3], blk.block[5]
-                T = B * H * W
-                a_hi, a_lo = em.pair("act", (T, C))
-                h_hi, h_lo = em.pair("hid", (T, 4 * C))
-                if "w1g" in pk:
-                    stats = em.buf("ln_stats", (T, C // 32, 2), torch.float32)
-                    ops.dwconv7_stats(res, pk["w49"], dw.bias.detach(), a_hi, stats, plan=plan)
-                    ops.gemm_ln_gelu(a_hi, pk["w1g"], T, 4 * C, C, stats, C // 32, pk["w1g_sum"], pk["b1f"], h_hi,
-                                     eps=ln.eps, plan=plan)
-                else:
-                    ops.dwconv7_ln(res, pk["w49"], dw.bias.detach(), ln.weight.detach(), ln.bias.detach(), a_hi, a_lo,
-                                   eps=ln.eps, plan=plan)
-                    ops.gemm_bf16(a_hi, pk["w1"], T, 4 * C, C, a_lo=a_lo, bw_lo=pk["w1_lo"], bias=fc1.bias.detach(),
-                                  out_bf16=h_hi, out_bf16_lo=h_lo, act=_lib.ACT_GELU, plan=plan)
-                ops.gemm_bf16(h_hi, pk["w2"], T, C, 4 * C, a_lo=h_lo, bw_lo=pk["w2_lo"], bias=fc2.bias.detach(),
-                              scale=blk.layer_scale.detach().view(C), res_f32=res, out_f32=res, plan=plan)
+                j = i
+                while j < len(steps) and steps[j][0][0] == "block":
+                    j += 1
+                self._emit_stage(em, steps[i:j], res, B, H, W, C)
+                i = j
             else:
                 _, ln, conv = s
                 stride = conv.stride[0]
@@ -144,4 +143,44 @@ class ConvNeXtProgram:
                 ops.gemm_bf16(i_hi, pk["w"], M, Cn, 4 * C, a_lo=i_lo, bw_lo=pk["w_lo"], bias=conv.bias.detach(),
                               out_f32=nxt, plan=plan)
                 res, H, W, C = nxt, Ho, Wo, Cn
+                i += 1
         return res.view(B * H * W, C), H, W, C
+
+    def _emit_stage(self, em: Emit, blocks, res: torch.Tensor, B: int, H: int, W: int, C: int) -> None:
+        """The CNBlocks of one stage (same H, W, C), updating the fp32 residual stream `res` in place.
+
+        bf16 mode runs the whole stage image chunk by image chunk (images are independent in the forward), with the
+        chunk sized so that its working set - fp32 residual, bf16 conv output, bf16 hidden activations, 16 bytes per
+        element - stays in the 126 MB L2 across the kernels and across the blocks of the stage, instead of
+        round-tripping through HBM after every kernel."""
+        plan = em.plan
+        T = B * H * W
+        a_hi, a_lo = em.pair("act", (T, C))
+        h_hi, h_lo = em.pair("hid", (T, 4 * C))
+        folded = all("w1g" in pk for _, pk in blocks)
+        if not folded:
+            for s, pk in blocks:
+                blk = s[1]
+                dw, ln, fc1, fc2 = blk.block[0], blk.block[2], blk.block[3], blk.block[5]
+                ops.dwconv7_ln(res, pk["w49"], dw.bias.detach(), ln.weight.detach(), ln.bias.detach(), a_hi, a_lo,
+                               eps=ln.eps, plan=plan)
+                ops.gemm_bf16(a_hi, pk["w1"], T, 4 * C, C, a_lo=a_lo, bw_lo=pk["w1_lo"], bias=fc1.bias.detach(),
+                              out_bf16=h_hi, out_bf16_lo=h_lo, act=_lib.ACT_GELU, plan=plan)
+                ops.gemm_bf16(h_hi, pk["w2"], T, C, 4 * C, a_lo=h_lo, bw_lo=pk["w2_lo"], bias=fc2.bias.detach(),
+                              scale=blk.layer_scale.detach().view(C), res_f32=res, out_f32=res, plan=plan)
+            return
+        stats = em.buf("ln_stats", (T, C // 32, 2), torch.float32)
+        nb = max(1, min(B, int(L2_CHUNK_BYTES // (16 * H * W * C))))
+        res4, res2 = res.view(B, H, W, C), res.view(T, C)
+        for b0 in range(0, B, nb):
+            b1 = min(B, b0 + nb)
+            t0, t1 = b0 * H * W, b1 * H * W
+            for s, pk in blocks:
+                blk = s[1]
+                dw, ln, fc2 = blk.block[0], blk.block[2], blk.block[5]
+                ops.dwconv7_stats(res4[b0:b1], pk["w49"], dw.bias.detach(), a_hi[t0:t1], stats[t0:t1], plan=plan)
+                ops.gemm_ln_gelu(a_hi[t0:t1], pk["w1g"], t1 - t0, 4 * C, C, stats[t0:t1], C // 32, pk["w1g_sum"],
+                                 pk["b1f"], h_hi[t0:t1], eps=ln.eps, plan=plan)
+                ops.gemm_bf16(h_hi[t0:t1], pk["w2"], t1 - t0, C, 4 * C, bias=fc2.bias.detach(),
+                              scale=blk.layer_scale.detach().view(C), res_f32=res2[t0:t1], out_f32=res2[t0:t1],
+                              plan=plan)
