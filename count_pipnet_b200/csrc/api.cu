@@ -523,6 +523,20 @@ int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bia
     if (blocks > cap) blocks = cap;
     const int grid = static_cast<int>(blocks);
     set_info("stem_ln", 2.0 * 48 * 96 * B * Ho * Wo, 4.0 * B * (3.0 * H * W + 96.0 * Ho * Wo), "B=%d H=%d W=%d", B, H, W);
+    const size_t smem2 = (12 * 96 * 4 + 2 * 12 * 4 * static_cast<size_t>(Wo)) * sizeof(float);
+    if (W % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && smem2 <= 160 * 1024 && getenv("CPN_STEM_V1") == nullptr) {
+        long long rows = static_cast<long long>(B) * Ho;
+        const long long cap2 = 2LL * num_sms();  // 124 registers x 256 threads: two resident CTAs per SM
+        const int grid2 = static_cast<int>(rows < cap2 ? rows : cap2);
+        return submit(plan, stream, [=](cudaStream_t st) -> int {
+            if (smem2 > 48 * 1024)
+                CPN_CUDA(cudaFuncSetAttribute(cpn::stem_ln_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(smem2)));
+            cpn::stem_ln_rows_kernel<<<grid2, cpn::STEM2_THREADS, smem2, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
+            CPN_CUDA(cudaGetLastError());
+            return 0;
+        });
+    }
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         cpn::stem_ln_kernel<<<grid, cpn::STEM_WARPS * 32, 0, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
         CPN_CUDA(cudaGetLastError());

@@ -115,6 +115,116 @@ stem_ln_kernel(const float* __restrict__ x, const float* __restrict__ w, const f
     }
 }
 
+// Second stem kernel (used when W % 4 == 0): a persistent CTA walks output rows (b, ho). The 12 input row segments
+// of a row (3 channels x 4 kernel rows, 4*Wo floats each) arrive by cp.async one row ahead (double buffer), the
+// weights sit in shared memory as [c*4+kh][n][kw] so that a lane's four kw taps are one 16-byte load, and a thread
+// computes 4 tokens x 6 channels (channels cg, cg+16, ..., cg+80): per (c,kh) step 4 broadcast input loads + 6 weight
+// loads feed 96 FMAs. LayerNorm (two passes, as the reference) reduces over the 16 lanes that share a token.
+constexpr int STEM2_THREADS = 256;
+
+__device__ __forceinline__ float half_warp_sum(float v) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(STEM2_THREADS)
+stem_ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                    const float* __restrict__ ln_w, const float* __restrict__ ln_b, float* __restrict__ out, int B,
+                    int H, int W, int Ho, int Wo, float eps) {
+    extern __shared__ __align__(16) float stem_smem[];
+    float* ws = stem_smem;                      // [12][96][4]
+    const int rowf = 12 * 4 * Wo;               // floats of one staged output row
+    float* inb = stem_smem + 12 * 96 * 4;       // [2][12][4 * Wo]
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < STEM_COUT * STEM_K; idx += STEM2_THREADS) {
+        const int n = idx / STEM_K, k = idx - n * STEM_K;
+        ws[((k >> 2) * STEM_COUT + n) * 4 + (k & 3)] = __ldg(w + idx);
+    }
+    const int cg = tid & 15, tq = tid >> 4;
+    float br[6], gw[6], gb[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        br[i] = __ldg(bias + i * 16 + cg);
+        gw[i] = __ldg(ln_w + i * 16 + cg);
+        gb[i] = __ldg(ln_b + i * 16 + cg);
+    }
+    const int nrows = B * Ho;
+    auto issue = [&](int r, int buf) {
+        const int b = r / Ho, ho = r - b * Ho;
+        const uint32_t dst0 = ptx::smem_u32(inb + buf * rowf);
+        for (int j = tid; j < 12 * Wo; j += STEM2_THREADS) {
+            const int seg = j / Wo, q = j - seg * Wo;
+            const int c = seg >> 2, kh = seg & 3;
+            const float* src = x + ((static_cast<size_t>(b) * 3 + c) * H + (4 * ho + kh)) * W + 4 * q;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + (seg * 4 * Wo + 4 * q) * 4), "l"(src)
+                         : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int r = blockIdx.x;
+    if (r < nrows) issue(r, 0);
+    int buf = 0;
+    for (; r < nrows; r += gridDim.x, buf ^= 1) {
+        if (r + static_cast<int>(gridDim.x) < nrows) {
+            issue(r + gridDim.x, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();  // this row's inputs (and, the first time, the weights) are visible to every thread
+        const float* in = inb + buf * rowf;
+        float* orow = out + static_cast<size_t>(r) * Wo * STEM_COUT;
+        for (int t0 = 0; t0 < Wo; t0 += 64) {
+            int tok[4];
+#pragma unroll
+            for (int tt = 0; tt < 4; ++tt) tok[tt] = min(t0 + tq * 4 + tt, Wo - 1);
+            float acc[4][6];
+#pragma unroll
+            for (int tt = 0; tt < 4; ++tt)
+#pragma unroll
+                for (int i = 0; i < 6; ++i) acc[tt][i] = br[i];
+#pragma unroll 2
+            for (int ckh = 0; ckh < 12; ++ckh) {
+                float4 a[4], wv[6];
+#pragma unroll
+                for (int tt = 0; tt < 4; ++tt) a[tt] = *reinterpret_cast<const float4*>(in + ckh * 4 * Wo + 4 * tok[tt]);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) wv[i] = *reinterpret_cast<const float4*>(ws + (ckh * STEM_COUT + i * 16 + cg) * 4);
+#pragma unroll
+                for (int tt = 0; tt < 4; ++tt)
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) {
+                        acc[tt][i] = fmaf(a[tt].x, wv[i].x, acc[tt][i]);
+                        acc[tt][i] = fmaf(a[tt].y, wv[i].y, acc[tt][i]);
+                        acc[tt][i] = fmaf(a[tt].z, wv[i].z, acc[tt][i]);
+                        acc[tt][i] = fmaf(a[tt].w, wv[i].w, acc[tt][i]);
+                    }
+            }
+#pragma unroll
+            for (int tt = 0; tt < 4; ++tt) {
+                float s = 0.f;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) s += acc[tt][i];
+                const float mean = half_warp_sum(s) * (1.0f / STEM_COUT);
+                float ss = 0.f;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    acc[tt][i] -= mean;
+                    ss = fmaf(acc[tt][i], acc[tt][i], ss);
+                }
+                const float rstd = rsqrtf(half_warp_sum(ss) * (1.0f / STEM_COUT) + eps);
+                if (t0 + tq * 4 + tt < Wo) {
+                    float* o = orow + static_cast<size_t>(tok[tt]) * STEM_COUT + cg;
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) o[i * 16] = acc[tt][i] * rstd * gw[i] + gb[i];
+                }
+            }
+        }
+        __syncthreads();  // everyone is done with this buffer before the next iteration's prefetch overwrites it
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ dwconv7 + LN
 // CTA = (column strip of TW tokens, row segment, image); thread = one channel pair; it marches down the input rows
 // keeping the 7 in-flight output rows in registers, so every loaded input feeds 7*TW packed FMAs and the 49 weights

@@ -89,15 +89,15 @@ def test_gemm_split_fp32_mode(cuda_device):
     assert rel < 5e-5, rel
 
 
-def test_stem_ln(cuda_device):
+@pytest.mark.parametrize("B,H,W", [(3, 64, 96), (2, 224, 224), (1, 448, 448), (2, 36, 52), (5, 8, 8), (2, 30, 41)])
+def test_stem_ln(cuda_device, B, H, W):
     g = torch.Generator().manual_seed(5)
-    B, H, W = 3, 64, 96
     x = torch.randn(B, 3, H, W, generator=g).to(cuda_device)
     w = (torch.randn(96, 3, 4, 4, generator=g) * 0.2).to(cuda_device)
     b = torch.randn(96, generator=g).to(cuda_device)
     lw = torch.rand(96, generator=g).to(cuda_device) + 0.5
     lb = torch.randn(96, generator=g).to(cuda_device)
-    out = torch.empty(B, H // 4, W // 4, 96, device=cuda_device)
+    out = torch.full((B, H // 4, W // 4, 96), float("nan"), device=cuda_device)
     ops.stem_ln(x, w.reshape(96, 48).contiguous(), b, lw, lb, out)
     torch.backends.cudnn.allow_tf32 = False
     y = F.conv2d(x, w, b, stride=4).permute(0, 2, 3, 1)
