@@ -324,6 +324,8 @@ int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, 
     g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
     static const int order = [] { const char* e = getenv("CPN_GEMM_ORDER"); return e == nullptr ? 0 : atoi(e); }();
     g.p.m_fastest = order;
+    static const int dbg = [] { const char* e = getenv("CPN_GEMM_DBG"); return e == nullptr ? 0 : atoi(e); }();
+    g.p.dbg = dbg;
     const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
     const int slots = num_sms() / g.cg;
     g.grid = g.cg * (tiles < slots ? tiles : slots);
@@ -433,7 +435,14 @@ namespace {
 template <int C>
 int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
                int nstrips, int rows, dim3 grid, cudaStream_t st) {
-    cpn::dwconv7_stats_kernel<C><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+    // register cap = occupancy: 200 -> 10 warps per SM, 168 -> 12 (light spilling), 224 -> 8 (CPN_DWS_REGS, tuning)
+    static const int regs = [] { const char* e = getenv("CPN_DWS_REGS"); return e == nullptr ? 200 : atoi(e); }();
+    if (regs <= 168)
+        cpn::dwconv7_stats_kernel<C, 168><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+    else if (regs <= 200)
+        cpn::dwconv7_stats_kernel<C, 200><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+    else
+        cpn::dwconv7_stats_kernel<C, 224><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -605,7 +614,7 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
     // row segments: every segment pays 6 halo rows of loads AND of FMAs (the body is branch-free), so split H only
     // when the grid would not give each SM its two resident CTAs a few times over
     int nseg = 1;
-    while (static_cast<long long>(gx) * nseg * B < 6LL * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
+    while (static_cast<long long>(gx) * nseg * B < 5LL * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
     if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knobs (tools/run_op.py)
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;

@@ -30,7 +30,8 @@
 
 namespace cpn {
 
-constexpr int DWS_WARPS = 4;   // warps per CTA (independent of each other)
+constexpr int DWS_WARPS = 2;   // warps per CTA (independent of each other)
+constexpr int DWS_CTAS_PER_SM = 5;  // 10 warps per SM at <= 204 registers: B=64 then needs 2 / 2 / 2 / 4 waves per stage
 constexpr int DWS_TW = 4;      // output columns per lane
 constexpr int DWS_DEPTH = 3;   // rows in flight ahead of the one being consumed
 constexpr int DWS_NSLOT = DWS_DEPTH + 1;
@@ -52,8 +53,8 @@ struct StaticFor<N, N> {
 
 __device__ __forceinline__ float2 ldg_f2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
-template <int C>
-__global__ void __launch_bounds__(DWS_WARPS * 32, 2)
+template <int C, int MAXREG>
+__global__ void __launch_bounds__(DWS_WARPS * 32) __maxnreg__(MAXREG)
 dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49, const float* __restrict__ bias,
                      __nv_bfloat16* __restrict__ out, float* __restrict__ stats, int H, int W, int nstrips,
                      int rows_per_seg) {

@@ -40,6 +40,7 @@ struct Gemm2Params {
     // tile order: 0 = consecutive tiles walk the N blocks of one M block (co-running CTAs share the A tile),
     // 1 = consecutive tiles walk the M blocks of one N block (co-running CTAs share the B tile)
     int m_fastest;
+    int dbg;  // timing experiments only (CPN_GEMM_DBG): bit 0 = epilogue skips its math, bit 1 = MMA thread skips the MMAs
 };
 
 // CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cluster of two, tcgen05 cta_group::2) per 256 x BN tile;
@@ -167,6 +168,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     const uint64_t bdesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_b(stage)));
 #pragma unroll
                     for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k) {
+                        if (p.dbg & 2) continue;
                         if (CG == 2) ptx::umma_bf16_2sm(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                         else ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                     }
@@ -290,10 +292,11 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                             v2 = fadd2(v2, make_float2(b1.x, b1.y));
                             v3 = fadd2(v3, make_float2(b1.z, b1.w));
                         }
-                        const float2 y0 = gelu_sat2(v0);
-                        const float2 y1 = gelu_sat2(v1);
-                        const float2 y2 = gelu_sat2(v2);
-                        const float2 y3 = gelu_sat2(v3);
+                        const bool raw = (p.dbg & 1) != 0;
+                        const float2 y0 = raw ? v0 : gelu_sat2(v0);
+                        const float2 y1 = raw ? v1 : gelu_sat2(v1);
+                        const float2 y2 = raw ? v2 : gelu_sat2(v2);
+                        const float2 y3 = raw ? v3 : gelu_sat2(v3);
                         ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
                                     make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
                     }
