@@ -292,6 +292,10 @@ int launch_gemm2(const Gemm2Launch& g, int bn, int epi, cudaStream_t st) {
 int pick_bn2(int M, int N, int epi) {
     static const int cands[] = {256, 192, 128, 96, 64, 32};
     const int chunk = cpn::epi_out_bf16(epi) ? 64 : 32;
+    if (const char* e = getenv("CPN_GEMM_BN")) {  // tuning knob (tools/run_op.py)
+        const int bn = atoi(e);
+        if (bn > 0 && N % bn == 0 && bn % chunk == 0 && (bn == 256 || bn == 192 || bn == 128 || bn == 64)) return bn;
+    }
     const int m_blocks = (M + cpn::GEMM_BM - 1) / cpn::GEMM_BM;
     int best = 0;
     for (int bn : cands) {
@@ -669,7 +673,7 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
     set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2),
              "B=%d H=%d W=%d C=%d s=%d", B, H, W, C, stride);
-    if (lo == nullptr && C % 4 == 0 && C <= 768) {
+    if (lo == nullptr && C % 4 == 0 && C <= 768 && ntok < (1LL << 31) - 65536) {
         // bf16 mode: vectorised persistent kernel, two tokens in flight per warp
         const int nv = (C / 4 + 31) / 32;
         long long want = (ntok + 15) / 16;

@@ -410,8 +410,8 @@ ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
                        __nv_bfloat16* __restrict__ out, int B, int H, int W, int C, int stride, int Ho, int Wo,
                        float eps) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long ntok = static_cast<long long>(B) * H * W;
-    const long long nwarps = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
+    const int ntok = B * H * W;  // < 2^31 (checked by the host): 32-bit index arithmetic, no 64-bit divisions
+    const int nwarps = gridDim.x * (blockDim.x >> 5);
     const int nchunk = C >> 2;  // float4 chunks per token
     float4 gw[NV], gb[NV];
     bool act[NV];
@@ -422,12 +422,12 @@ ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
         gb[i] = act[i] ? __ldg(reinterpret_cast<const float4*>(ln_b) + lane + 32 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     const float inv_c = 1.0f / static_cast<float>(C);
-    for (long long t = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + warp) * 2; t < ntok; t += 2 * nwarps) {
+    for (int t = (blockIdx.x * (blockDim.x >> 5) + warp) * 2; t < ntok; t += 2 * nwarps) {
         const int ntk = t + 1 < ntok ? 2 : 1;
         float4 v[2][NV];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            const float4* xr = reinterpret_cast<const float4*>(x + (t + (u < ntk ? u : 0)) * C);
+            const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(t + (u < ntk ? u : 0)) * C);
 #pragma unroll
             for (int i = 0; i < NV; ++i) v[u][i] = act[i] ? __ldg(xr + lane + 32 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
@@ -453,16 +453,22 @@ ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
                 pk[i].x = pack_bf16x2(fmaf(v[u][i].x * rstd, gw[i].x, gb[i].x), fmaf(v[u][i].y * rstd, gw[i].y, gb[i].y));
                 pk[i].y = pack_bf16x2(fmaf(v[u][i].z * rstd, gw[i].z, gb[i].z), fmaf(v[u][i].w * rstd, gw[i].w, gb[i].w));
             }
-            const long long tok = t + u;
-            const int w = static_cast<int>(tok % W);
-            const int h = static_cast<int>((tok / W) % H);
-            const int b = static_cast<int>(tok / (static_cast<long long>(W) * H));
+            const int tok = t + u;
+            const int row = tok / W;
+            const int w = tok - row * W;
+            const int b = row / H;
+            const int h = row - b * H;
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
                 const int kh = kk >> 1, kw = kk & 1;
                 const int hh = h - kh, ww = w - kw;
-                if (hh < 0 || ww < 0 || (hh % stride) != 0 || (ww % stride) != 0) continue;
-                const int ho = hh / stride, wo = ww / stride;
+                if (hh < 0 || ww < 0) continue;
+                int ho = hh, wo = ww;
+                if (stride == 2) {
+                    if ((hh | ww) & 1) continue;
+                    ho = hh >> 1;
+                    wo = ww >> 1;
+                }
                 if (ho >= Ho || wo >= Wo) continue;
                 uint2* o = reinterpret_cast<uint2*>(out + ((static_cast<size_t>(b) * Ho + ho) * Wo + wo) * (4 * static_cast<size_t>(C)) +
                                                     static_cast<size_t>(kk) * C);
