@@ -225,22 +225,22 @@ struct Gemm2Launch {
     int cg;  // 1: one CTA per 128-row tile; 2: CTA pairs (cta_group::2) on 256-row tiles
 };
 
-template <int BN, int EPI, int CG>
+template <int BN, int EPI, int CG, int EW = cpn::GEMM_EPI_WARPS>
 int launch_gemm2_inst(const Gemm2Launch& g, cudaStream_t st) {
-    using S = cpn::Gemm2Cfg<BN, EPI, CG>;
-    auto kern = cpn::gemm_tma_epi_kernel<BN, EPI, CG>;
+    using S = cpn::Gemm2Cfg<BN, EPI, CG, EW>;
+    auto kern = cpn::gemm_tma_epi_kernel<BN, EPI, CG, EW>;
     static bool attr_done = false;
     if (!attr_done) {
         CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         attr_done = true;
     }
     if (CG == 1) {
-        kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
+        kern<<<g.grid, S::THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
     } else {
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
         cfg.gridDim = dim3(g.grid);
-        cfg.blockDim = dim3(cpn::GEMM_THREADS);
+        cfg.blockDim = dim3(S::THREADS);
         cfg.dynamicSmemBytes = S::TOTAL;
         cfg.stream = st;
         cudaLaunchAttribute attr[1];
@@ -265,6 +265,20 @@ int launch_gemm2_bn(const Gemm2Launch& g, int bn, cudaStream_t st) {
             case 128: return launch_gemm2_inst<128, EPI, 2>(g, st);
         }
         return fail("no CTA-pair GEMM instantiation for BN=%d", bn);
+    }
+    if (cpn::epi_out_bf16(EPI)) {
+        // bf16-output (GELU) epilogues: CPN_GEMM_EW=16 selects 16 epilogue warps. Measured: no gain at K=384 (0.0736 vs
+        // 0.0716 ms) and a loss at K=768 (0.235 vs 0.193 ms), so 8 stays the default (profiles/r01_gemm_pairs.md).
+        static const int ew = [] { const char* e = getenv("CPN_GEMM_EW"); return e == nullptr ? 8 : atoi(e); }();
+        constexpr int EPB = cpn::epi_out_bf16(EPI) ? EPI : cpn::EPI_GELU_BF16;
+        if (ew == 16) {
+            switch (bn) {
+                case 256: return launch_gemm2_inst<256, EPB, 1, 16>(g, st);
+                case 192: return launch_gemm2_inst<192, EPB, 1, 16>(g, st);
+                case 128: return launch_gemm2_inst<128, EPB, 1, 16>(g, st);
+                case 64: return launch_gemm2_inst<64, EPB, 1, 16>(g, st);
+            }
+        }
     }
     switch (bn) {
         case 256: return launch_gemm2_inst<256, EPI, 1>(g, st);

@@ -40,12 +40,12 @@ struct Gemm2Params {
     // tile order: 0 = consecutive tiles walk the N blocks of one M block (co-running CTAs share the A tile),
     // 1 = consecutive tiles walk the M blocks of one N block (co-running CTAs share the B tile)
     int m_fastest;
-    int dbg;  // timing experiments only (CPN_GEMM_DBG): bit 0 = epilogue skips its math, bit 1 = MMA thread skips the MMAs
+    int dbg;  // timing experiments only (CPN_GEMM_DBG): bit 1 = MMA thread skips the MMAs, bit 2 = epilogue skips its TMA stores
 };
 
 // CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cluster of two, tcgen05 cta_group::2) per 256 x BN tile;
 // each CTA stages its own 128 rows of A and HALF of the B tile, so operand traffic from L2 per FLOP drops by a third.
-template <int BN, int EPI, int CG = 1>
+template <int BN, int EPI, int CG = 1, int EW = GEMM_EPI_WARPS>
 struct Gemm2Cfg {
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
     static constexpr int B_BYTES = (BN / CG) * GEMM_BK * 2;
@@ -53,8 +53,12 @@ struct Gemm2Cfg {
     static constexpr int CHUNK_COLS = epi_out_bf16(EPI) ? 64 : 32;  // 128 bytes of output per row
     static constexpr int NCHUNK = BN / CHUNK_COLS;
     static constexpr int STG_BLOCK = 32 * 128;                        // one chunk: 32 rows x 128 B
-    static constexpr int STAGING_BYTES = GEMM_EPI_WARPS * 2 * STG_BLOCK;  // two blocks per epilogue warp
-    static constexpr int BAR_BYTES = (2 * 8 + 4 + 2 * GEMM_EPI_WARPS) * 8 + 16;
+    static constexpr int NGRP = EW / 4;                               // epilogue warps per 32-row TMEM lane quarter
+    static constexpr int NBUF = EW == 8 ? 2 : 1;                      // staging blocks per epilogue warp (64 KB in total)
+    static constexpr int THREADS = 128 + 32 * EW;
+    static constexpr int STAGING_BYTES = EW * NBUF * STG_BLOCK;
+    static constexpr int BAR_BYTES = (2 * 8 + 4 + 2 * EW) * 8 + 16;
+    static_assert(EW == 8 || (EW == 16 && epi_out_bf16(EPI)), "16 epilogue warps: bf16-output epilogues only");
     static constexpr int BUDGET = 227 * 1024 - 1024 - STAGING_BYTES - BAR_BYTES;
     static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
     static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
@@ -65,11 +69,14 @@ struct Gemm2Cfg {
     static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
 };
 
-template <int BN, int EPI, int CG = 1>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+// EW = epilogue warps (8 or 16). 16 (bf16-output epilogues) puts four epilogue warps on every scheduler: the LN+GELU
+// epilogue is issue-latency-bound with two (measured: fc1 of stage 3 takes 0.057 of its 0.071 ms with the MMAs and the
+// stores switched off), and a 64-column chunk is processed as two 32-column halves to stay under 102 registers.
+template <int BN, int EPI, int CG = 1, int EW = GEMM_EPI_WARPS>
+__global__ void __launch_bounds__(128 + 32 * EW, 1)
 gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_out, const Gemm2Params p) {
-    using S = Gemm2Cfg<BN, EPI, CG>;
+    using S = Gemm2Cfg<BN, EPI, CG, EW>;
     constexpr int STAGES = S::STAGES;
     static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N constraint for M=128");
     static_assert(CG == 1 || (CG == 2 && BN % 32 == 0), "a CTA pair splits the B tile in two halves of BN/2 rows");
@@ -85,7 +92,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint64_t* tmem_full_bar = empty_bar + 8;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint64_t* res_bar = tmem_empty_bar + 2;  // [epilogue warp][2]
-    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(res_bar + 2 * GEMM_EPI_WARPS);
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(res_bar + 2 * EW);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -102,9 +109,9 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(&tmem_full_bar[s], 1);
-            ptx::mbar_init(&tmem_empty_bar[s], CG * GEMM_EPI_WARPS);  // both CTAs' epilogues report to the leader
+            ptx::mbar_init(&tmem_empty_bar[s], CG * EW);  // both CTAs' epilogues report to the leader
         }
-        for (int s = 0; s < 2 * GEMM_EPI_WARPS; ++s) ptx::mbar_init(&res_bar[s], 1);
+        for (int s = 0; s < 2 * EW; ++s) ptx::mbar_init(&res_bar[s], 1);
         ptx::fence_mbar_init();
     } else if (warp == 2) {
         if (CG == 2) {
@@ -185,12 +192,13 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         __syncwarp();
     } else if (warp >= 4) {
-        // ------------------------------------------------------------ epilogue (8 warps)
+        // ------------------------------------------------------------ epilogue (EW warps)
+        constexpr int NGRP = S::NGRP, NBUF = S::NBUF;
         const int ew = warp - 4;
         const int q = warp & 3;    // TMEM lane quarter this warp may access = 32-row block of the tile
-        const int half = ew >> 2;  // this warp takes chunks half, half + 2, ...
-        const uint32_t stg = ptx::smem_u32(staging) + ew * 2 * S::STG_BLOCK;
-        uint8_t* stg_ptr = staging + ew * 2 * S::STG_BLOCK;
+        const int half = ew >> 2;  // this warp takes chunks half, half + NGRP, ...
+        const uint32_t stg = ptx::smem_u32(staging) + ew * NBUF * S::STG_BLOCK;
+        uint8_t* stg_ptr = staging + ew * NBUF * S::STG_BLOCK;
         uint64_t* rbar = res_bar + 2 * ew;
         const uint32_t sw = static_cast<uint32_t>(lane & 7);          // swizzle phase of this lane's row
         const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;  // this lane's row inside a staging block
@@ -238,11 +246,11 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             ptx::tc_fence_after();
             const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-            for (int c = half; c < S::NCHUNK; c += 2, ++g) {
-                const uint32_t b = g & 1;
+            for (int c = half; c < S::NCHUNK; c += NGRP, ++g) {
+                const uint32_t b = NBUF == 2 ? (g & 1) : 0;
                 const uint32_t buf = stg + b * S::STG_BLOCK + row_off;
                 const int col0 = col_tile + c * S::CHUNK_COLS;
-                const bool last = c + 2 >= S::NCHUNK;
+                const bool last = c + NGRP >= S::NCHUNK;
                 if (EPI == EPI_SCALE_RES_F32) {
                     if (!last) {
                         if (lane == 0) {
@@ -254,34 +262,36 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                         __syncwarp();
                     }
                 } else {
-                    if (lane == 0) ptx::bulk_wait_read<1>();  // the store that last used this block is done reading
+                    if (lane == 0) ptx::bulk_wait_read<NBUF - 1>();  // the store that last used this block is done reading
                     __syncwarp();
                 }
                 uint32_t r0[32];
                 ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS, r0);
                 if (epi_out_bf16(EPI)) {
-                    uint32_t r1[32];
-                    ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS + 32, r1);
-                    ptx::tmem_ld_wait();
-                    if (last) {
-                        ptx::tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) { if (CG == 2) ptx::mbar_arrive_leader(&tmem_empty_bar[as]); else ptx::mbar_arrive(&tmem_empty_bar[as]); }
-                    }
-                    // 64 columns -> gelu(acc + bias) -> 8 x 16 bytes of bf16
+                    // 64 columns as two halves of 32: gelu(acc + bias) -> 2 x 4 x 16 bytes of bf16
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const uint32_t* src = (j < 4) ? (r0 + 8 * j) : (r1 + 8 * (j - 4));
-                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
-                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
+                    for (int hh = 0; hh < 2; ++hh) {
+                        if (hh == 1) ptx::tmem_ld32(taddr_row + c * S::CHUNK_COLS + 32, r0);
+                        ptx::tmem_ld_wait();
+                        if (last && hh == 1) {
+                            ptx::tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) { if (CG == 2) ptx::mbar_arrive_leader(&tmem_empty_bar[as]); else ptx::mbar_arrive(&tmem_empty_bar[as]); }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                        const uint32_t* src = r0 + 8 * j;
+                        const int cj = col0 + 32 * hh + 8 * j;
+                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + cj));
+                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + cj + 4));
                         float2 v0 = make_float2(__uint_as_float(src[0]), __uint_as_float(src[1]));
                         float2 v1 = make_float2(__uint_as_float(src[2]), __uint_as_float(src[3]));
                         float2 v2 = make_float2(__uint_as_float(src[4]), __uint_as_float(src[5]));
                         float2 v3 = make_float2(__uint_as_float(src[6]), __uint_as_float(src[7]));
                         if (EPI == EPI_LN_GELU_BF16) {
                             // rstd * acc + (-mean * rstd * colsum + bias), two columns per instruction
-                            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j));
-                            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.colsum + col0 + 8 * j + 4));
+                            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.colsum + cj));
+                            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.colsum + cj + 4));
                             v0 = ffma2(v0, ln_rs2, ffma2(ln_nm2, make_float2(s0.x, s0.y), make_float2(b0.x, b0.y)));
                             v1 = ffma2(v1, ln_rs2, ffma2(ln_nm2, make_float2(s0.z, s0.w), make_float2(b0.z, b0.w)));
                             v2 = ffma2(v2, ln_rs2, ffma2(ln_nm2, make_float2(s1.x, s1.y), make_float2(b1.x, b1.y)));
@@ -292,13 +302,13 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                             v2 = fadd2(v2, make_float2(b1.x, b1.y));
                             v3 = fadd2(v3, make_float2(b1.z, b1.w));
                         }
-                        const bool raw = (p.dbg & 1) != 0;
-                        const float2 y0 = raw ? v0 : gelu_sat2(v0);
-                        const float2 y1 = raw ? v1 : gelu_sat2(v1);
-                        const float2 y2 = raw ? v2 : gelu_sat2(v2);
-                        const float2 y3 = raw ? v3 : gelu_sat2(v3);
-                        ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
+                        const float2 y0 = gelu_sat2(v0);
+                        const float2 y1 = gelu_sat2(v1);
+                        const float2 y2 = gelu_sat2(v2);
+                        const float2 y3 = gelu_sat2(v3);
+                        ptx::sts_u4(buf + ((static_cast<uint32_t>(4 * hh + j) ^ sw) << 4),
                                     make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
+                    }
                     }
                 } else {
                     ptx::tmem_ld_wait();
@@ -327,7 +337,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 }
                 ptx::fence_proxy_async();  // generic-proxy writes -> visible to the TMA store
                 __syncwarp();
-                if (lane == 0) {
+                if (lane == 0 && !(p.dbg & 4)) {
                     ptx::tma_store_2d(&tmap_out, stg_ptr + b * S::STG_BLOCK, col0, row0);
                     ptx::bulk_commit();
                 }
