@@ -811,36 +811,62 @@ int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const f
     });
 }
 
-int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
-                     float* partial, int B, int HW, int P, int chunks, void* stream) {
+int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
+                         float* partial, int* partial_arg, int B, int HW, int P, int chunks, void* stream) {
     if (chunks <= 0 || B <= 0 || B > 65535) return fail("cpn_softmax_pool: bad chunks/B");
-    const size_t smem = 8 * static_cast<size_t>(P) * sizeof(float);
+    const bool arg = partial_arg != nullptr && mode == CPN_POOL_MAX;
+    const size_t smem = 8 * static_cast<size_t>(P) * sizeof(float) * (arg ? 2 : 1);
     if (smem > 200 * 1024) return fail("cpn_softmax_pool: P=%d too large", P);
     const dim3 grid(chunks, B);
     set_info("softmax_pool", 4.0 * B * HW * P, 4.0 * B * HW * P * (1 + (gumbel != nullptr) + (map != nullptr)));
     if (gumbel == nullptr && !hard && map == nullptr && P % 128 == 0 && P <= 1024) {
-        // plain softmax, map not requested: register-resident kernel (smem <= 32 KB)
+        // plain softmax, map not requested: register-resident kernel
         const int nv = P / 128;
         return submit(plan, stream, [=](cudaStream_t st) -> int {
+#define CPN_SMP_CASE(NVV)                                                                                              \
+    case NVV:                                                                                                          \
+        if (arg) {                                                                                                     \
+            if (smem > 48 * 1024)                                                                                      \
+                CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_reg_kernel<NVV, true>,                                 \
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));   \
+            cpn::softmax_pool_reg_kernel<NVV, true><<<grid, 256, smem, st>>>(z, mode, partial, partial_arg, HW, chunks); \
+        } else {                                                                                                       \
+            cpn::softmax_pool_reg_kernel<NVV, false><<<grid, 256, smem, st>>>(z, mode, partial, nullptr, HW, chunks);  \
+        }                                                                                                              \
+        break;
             switch (nv) {
-                case 1: cpn::softmax_pool_reg_kernel<1><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 2: cpn::softmax_pool_reg_kernel<2><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 3: cpn::softmax_pool_reg_kernel<3><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 4: cpn::softmax_pool_reg_kernel<4><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 5: cpn::softmax_pool_reg_kernel<5><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 6: cpn::softmax_pool_reg_kernel<6><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                case 7: cpn::softmax_pool_reg_kernel<7><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
-                default: cpn::softmax_pool_reg_kernel<8><<<grid, 256, smem, st>>>(z, mode, partial, HW, chunks); break;
+                CPN_SMP_CASE(1) CPN_SMP_CASE(2) CPN_SMP_CASE(3) CPN_SMP_CASE(4)
+                CPN_SMP_CASE(5) CPN_SMP_CASE(6) CPN_SMP_CASE(7) CPN_SMP_CASE(8)
             }
+#undef CPN_SMP_CASE
             CPN_CUDA(cudaGetLastError());
             return 0;
         });
     }
+    int* parg = arg ? partial_arg : nullptr;
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(smem)));
-        cpn::softmax_pool_kernel<<<grid, 256, smem, st>>>(z, gumbel, tau, hard, mode, map, partial, HW, P, chunks);
+        cpn::softmax_pool_kernel<<<grid, 256, smem, st>>>(z, gumbel, tau, hard, mode, map, partial, parg, HW, P, chunks);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
+int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
+                     float* partial, int B, int HW, int P, int chunks, void* stream) {
+    return cpn_softmax_pool_arg(plan, z, gumbel, tau, hard, mode, map, partial, nullptr, B, HW, P, chunks, stream);
+}
+
+int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* partial_arg, int chunks, int* arg_out, int B,
+                           int P, void* stream) {
+    if (partial == nullptr || partial_arg == nullptr || arg_out == nullptr || chunks <= 0 || B <= 0 || B > 65535)
+        return fail("cpn_pool_argmax_reduce: bad argument");
+    const dim3 grid((P + 127) / 128, B);
+    set_info("pool_argmax", 0.0, 8.0 * B * chunks * P + 4.0 * B * P);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::pool_argmax_reduce_kernel<<<grid, 128, 0, st>>>(partial, partial_arg, chunks, arg_out, P);
         CPN_CUDA(cudaGetLastError());
         return 0;
     });

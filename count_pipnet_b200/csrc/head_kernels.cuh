@@ -42,8 +42,9 @@ enum PoolMode : int { POOL_MAX = 0, POOL_SUM = 1 };
 // partial: [B, chunks, P]
 __global__ void __launch_bounds__(256)
 softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbel, float tau, int hard, int mode,
-                    float* __restrict__ map, float* __restrict__ partial, int HW, int P, int chunks) {
-    extern __shared__ float s_pool[];  // [warps][P]
+                    float* __restrict__ map, float* __restrict__ partial, int* __restrict__ partial_arg, int HW, int P,
+                    int chunks) {
+    extern __shared__ float s_pool[];  // [warps][P] (+ [warps][P] arg-max tokens when partial_arg is given)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const int b = blockIdx.y;
@@ -52,7 +53,13 @@ softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbe
     const int t0 = chunk * per_chunk;
     const int t1 = min(HW, t0 + per_chunk);
     float* my_pool = s_pool + warp * P;
-    for (int p = lane; p < P; p += 32) my_pool[p] = 0.f;  // probabilities are >= 0, so 0 is neutral for max and sum
+    int* s_arg = reinterpret_cast<int*>(s_pool + wpb * P);
+    int* my_arg = s_arg + warp * P;
+    const bool want_arg = partial_arg != nullptr && mode == POOL_MAX;
+    for (int p = lane; p < P; p += 32) {
+        my_pool[p] = 0.f;  // probabilities are >= 0, so 0 is neutral for max and sum
+        if (want_arg) my_arg[p] = 0x7fffffff;
+    }
     __syncwarp();
     for (int t = t0 + warp; t < t1; t += wpb) {
         const float* zr = z + (static_cast<size_t>(b) * HW + t) * P;
@@ -86,8 +93,14 @@ softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbe
             if (gr != nullptr) v = (v + __ldg(gr + static_cast<size_t>(p) * HW)) / tau;
             float y = expf(v - m) * inv_s;
             if (hard) y = ((p == am ? 1.0f : 0.0f) - y) + y;  // y_hard - y_soft + y_soft (straight-through form)
-            if (mode == POOL_MAX) my_pool[p] = fmaxf(my_pool[p], y);
-            else my_pool[p] += y;
+            if (mode == POOL_MAX) {
+                if (y > my_pool[p]) {  // strict: the first (lowest) token keeps a tie, as torch.max does
+                    my_pool[p] = y;
+                    if (want_arg) my_arg[p] = t;
+                }
+            } else {
+                my_pool[p] += y;
+            }
             if (map != nullptr) map[(static_cast<size_t>(b) * P + p) * HW + t] = y;
         }
     }
@@ -95,12 +108,37 @@ softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbe
     float* out = partial + (static_cast<size_t>(b) * chunks + chunk) * P;
     for (int p = threadIdx.x; p < P; p += blockDim.x) {
         float a = s_pool[p];
+        int ai = want_arg ? s_arg[p] : 0;
         for (int wv = 1; wv < wpb; ++wv) {
             const float o = s_pool[wv * P + p];
-            a = (mode == POOL_MAX) ? fmaxf(a, o) : a + o;
+            if (mode == POOL_MAX) {
+                const int oi = want_arg ? s_arg[wv * P + p] : 0;
+                if (o > a || (o == a && oi < ai)) { a = o; ai = oi; }
+            } else {
+                a += o;
+            }
         }
         out[p] = a;
+        if (want_arg) partial_arg[(static_cast<size_t>(b) * chunks + chunk) * P + p] = ai;
     }
+}
+
+// Per (image, prototype): token index (h * W + w) of the spatial maximum, from the per-chunk maxima and arg-maxima
+// (chunks are in token order, so the first chunk keeps a tie; 0x7fffffff marks "no token seen": all-zero rows -> 0).
+__global__ void pool_argmax_reduce_kernel(const float* __restrict__ partial, const int* __restrict__ partial_arg,
+                                          int chunks, int* __restrict__ arg_out, int P) {
+    const int b = blockIdx.y;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const size_t base = static_cast<size_t>(b) * chunks * P + p;
+    float a = partial[base];
+    int ai = partial_arg[base];
+    for (int c = 1; c < chunks; ++c) {
+        const float o = partial[base + static_cast<size_t>(c) * P];
+        const int oi = partial_arg[base + static_cast<size_t>(c) * P];
+        if (o > a || (o == a && oi < ai)) { a = o; ai = oi; }
+    }
+    arg_out[static_cast<size_t>(b) * P + p] = ai == 0x7fffffff ? 0 : ai;
 }
 
 // Register-resident variant for the common case (plain softmax, no map, P a multiple of 128 up to 1024): each lane
@@ -108,9 +146,10 @@ softmax_pool_kernel(const float* __restrict__ z, const float* __restrict__ gumbe
 // instruction), so the row max / sum are two warp reductions, the probabilities never leave registers and the running
 // spatial max / sum stays in registers too; two tokens are in flight per warp. Same grid and partial layout as above.
 // exp() is ex2.approx of a pre-scaled argument: relative error 2^-22, well inside the fp32-mode parity bar (1e-4).
-template <int NV>
+template <int NV, bool ARG>
 __global__ void __launch_bounds__(256)
-softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict__ partial, int HW, int chunks) {
+softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict__ partial,
+                        int* __restrict__ partial_arg, int HW, int chunks) {
     constexpr int P = NV * 128;
     extern __shared__ float s_pool[];  // [warps][P]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -122,8 +161,11 @@ softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict
     const int t1 = min(HW, t0 + per_chunk);
     constexpr float LOG2E = 1.4426950408889634f;
     float4 pool[NV];
+    int4 parg[ARG ? NV : 1];  // token of the running maximum (max pooling with ARG)
 #pragma unroll
     for (int i = 0; i < NV; ++i) pool[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // probabilities are >= 0
+#pragma unroll
+    for (int i = 0; i < (ARG ? NV : 1); ++i) parg[i] = make_int4(0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff);
     const float4* zb = reinterpret_cast<const float4*>(z + static_cast<size_t>(b) * HW * P) + lane;
     for (int t = t0 + 2 * warp; t < t1; t += 2 * wpb) {
         const bool two = t + 1 < t1;
@@ -152,7 +194,17 @@ softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict
             }
             s = warp_sum(s);
             const float inv_s = (u == 1 && !two) ? 0.f : 1.0f / s;  // the duplicate of an odd tail contributes nothing
-            if (mode == POOL_MAX) {
+            if (mode == POOL_MAX && ARG) {
+                const int tcur = t + u;  // strict comparisons: the lowest token keeps a tie (tokens come in order)
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    const float yx = v[u][i].x * inv_s, yy = v[u][i].y * inv_s, yz = v[u][i].z * inv_s, yw = v[u][i].w * inv_s;
+                    if (yx > pool[i].x) { pool[i].x = yx; parg[ARG ? i : 0].x = tcur; }
+                    if (yy > pool[i].y) { pool[i].y = yy; parg[ARG ? i : 0].y = tcur; }
+                    if (yz > pool[i].z) { pool[i].z = yz; parg[ARG ? i : 0].z = tcur; }
+                    if (yw > pool[i].w) { pool[i].w = yw; parg[ARG ? i : 0].w = tcur; }
+                }
+            } else if (mode == POOL_MAX) {
 #pragma unroll
                 for (int i = 0; i < NV; ++i) {
                     pool[i].x = fmaxf(pool[i].x, v[u][i].x * inv_s);
@@ -172,17 +224,31 @@ softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict
         }
     }
     float4* mine = reinterpret_cast<float4*>(s_pool + warp * P) + lane;
+    int* s_arg = reinterpret_cast<int*>(s_pool + wpb * P);
 #pragma unroll
     for (int i = 0; i < NV; ++i) mine[32 * i] = pool[i];
+    if (ARG) {
+        int4* marg = reinterpret_cast<int4*>(s_arg + warp * P) + lane;
+#pragma unroll
+        for (int i = 0; i < (ARG ? NV : 1); ++i) marg[32 * i] = parg[i];
+    }
     __syncthreads();
     float* out = partial + (static_cast<size_t>(b) * chunks + chunk) * P;
+    const bool want_arg = ARG && mode == POOL_MAX;
     for (int p = threadIdx.x; p < P; p += blockDim.x) {
         float a = s_pool[p];
+        int ai = want_arg ? s_arg[p] : 0;
         for (int wv = 1; wv < wpb; ++wv) {
             const float o = s_pool[wv * P + p];
-            a = (mode == POOL_MAX) ? fmaxf(a, o) : a + o;
+            if (mode == POOL_MAX) {
+                const int oi = want_arg ? s_arg[wv * P + p] : 0;
+                if (o > a || (o == a && oi < ai)) { a = o; ai = oi; }
+            } else {
+                a += o;
+            }
         }
         out[p] = a;
+        if (want_arg) partial_arg[(static_cast<size_t>(b) * chunks + chunk) * P + p] = ai;
     }
 }
 

@@ -105,8 +105,16 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
     partial = em.buf("partial", (B, chunks, P), torch.float32)
     pmap = em.buf("map", (B, P, Hf, Wf), torch.float32) if want_map else None
     mode = _lib.POOL_SUM if is_count else _lib.POOL_MAX
+    # per (image, prototype) location of the spatial maximum, on request (model.track_prototype_argmax): what the
+    # reference's visualisation search reads off the full map (util/vis_pipnet.py:209-274) without writing the map
+    want_arg = bool(getattr(model, "track_prototype_argmax", False)) and not is_count
+    parg = em.buf("partial_arg", (B, chunks, P), torch.int32) if want_arg else None
     ops.softmax_pool(z, partial, B, HW, P, chunks, gumbel=noise, tau=tau, hard=gumbel, mode=mode, map_out=pmap,
-                     plan=plan)
+                     partial_arg=parg, plan=plan)
+    argmax = None
+    if want_arg:
+        argmax = em.buf("argmax", (B, P), torch.int32)
+        ops.pool_argmax_reduce(partial, parg, chunks, argmax, B, P, plan=plan)
     cls = model._classification
     K, D = cls.weight.shape
     pooled = em.buf("pooled", (B, P), torch.float32)
@@ -116,7 +124,7 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
                   inference=inference, use_ste=bool(getattr(model, "_use_ste", False)),
                   max_count=int(getattr(model, "_max_count", 1)), encoding=enc, enc_w0=det(w0), enc_w1=det(w1),
                   enc_w2=det(w2), plan=plan)
-    return {"noise": noise, "map": pmap, "pooled": pooled, "logits": logits}
+    return {"noise": noise, "map": pmap, "pooled": pooled, "logits": logits, "argmax": argmax, "grid": (Hf, Wf)}
 
 
 class _Recorded:
@@ -149,7 +157,7 @@ def network_forward(model: nn.Module, xs: torch.Tensor, inference: bool = False)
         prog = _ensure_program(st, model._net, split)
         if _e.USE_PLANS:
             tau = _head_spec(model)[2]
-            key = (B, H, W, bool(inference), want_map, split, tau)
+            key = (B, H, W, bool(inference), want_map, split, tau, bool(getattr(model, "track_prototype_argmax", False)))
             sig = _ptr_sig(model)
             rec = st.plans.get(key)
             if rec is None or rec.sig != sig:
@@ -174,6 +182,10 @@ def network_forward(model: nn.Module, xs: torch.Tensor, inference: bool = False)
                 _fill_gumbel(st.buffers.get("gumbel", (B, P, Hf, Wf), torch.float32), model)
             outs = _emit_head(em, model, feat, B, Hf, Wf, C, bool(inference), want_map)
         proto = outs["map"].clone() if outs["map"] is not None else None
+        if outs.get("argmax") is not None:
+            # [B, P] int32 token index h * Wf + w of each prototype's maximum, and the patch grid it refers to
+            model.cpn_prototype_argmax = outs["argmax"].clone()
+            model.cpn_patch_grid = outs["grid"]
         return proto, outs["pooled"].clone(), outs["logits"].clone()
 
 

@@ -128,10 +128,17 @@ def addon_conv1x1(feat, w, b, z, T, Cc, P, plan=None):
 
 
 def softmax_pool(z, partial, B, HW, P, chunks, *, gumbel=None, tau=1.0, hard=False, mode=_lib.POOL_MAX, map_out=None,
-                 plan=None):
-    _need_cuda(z, partial, gumbel, map_out)
-    _lib.call("cpn_softmax_pool", _ph(plan), ptr(z), ptr(gumbel), float(tau), int(bool(hard)), int(mode), ptr(map_out),
-              ptr(partial), B, HW, P, chunks, _stream())
+                 partial_arg=None, plan=None):
+    """partial_arg [B,chunks,P] int32 (max pooling): token of every chunk maximum, see pool_argmax_reduce."""
+    _need_cuda(z, partial, gumbel, map_out, partial_arg)
+    _lib.call("cpn_softmax_pool_arg", _ph(plan), ptr(z), ptr(gumbel), float(tau), int(bool(hard)), int(mode),
+              ptr(map_out), ptr(partial), ptr(partial_arg), B, HW, P, chunks, _stream())
+
+
+def pool_argmax_reduce(partial, partial_arg, chunks, arg_out, B, P, plan=None):
+    """arg_out [B,P] int32: token (h * W + w) of each prototype's spatial maximum per image."""
+    _need_cuda(partial, partial_arg, arg_out)
+    _lib.call("cpn_pool_argmax_reduce", _ph(plan), ptr(partial), ptr(partial_arg), chunks, ptr(arg_out), B, P, _stream())
 
 
 def head_tail(partial, chunks, pooled_out, logits_out, cls_w, cls_b, B, P, D, K, *, mode=_lib.POOL_MAX,

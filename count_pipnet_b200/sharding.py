@@ -48,3 +48,23 @@ def gather_outputs(pooled: torch.Tensor, out: torch.Tensor, batch: int, group=No
         return torch.cat([full[r * per: r * per + (e - s)] for r, (s, e) in enumerate(bounds)], dim=0)
 
     return gather(pooled), gather(out)
+
+
+def gather_prototype_max(pooled: torch.Tensor, argmax: torch.Tensor, batch: int, group=None):
+    """Per-prototype max gather: for every prototype the best-scoring image of the FULL batch, its
+    score and the patch token of the maximum -- what the reference's top-k / visualisation search keeps per prototype
+    (util/vis_pipnet.py:209-274) when the batch is spread over ranks.
+
+    pooled [b, P] and argmax [b, P] are this rank's shard (rows in reference order). Returns (score [P], image [P]
+    int64 index into the full batch, token [P] int64). Ties go to the lowest image index, as torch.max over the
+    concatenated batch would. One all-gather of 2 * b * P values per rank; no map leaves its GPU."""
+    full_pooled, full_arg = gather_outputs(pooled, argmax.to(pooled.dtype), batch, group=group)
+    if full_pooled.shape[0] == 0:
+        raise ValueError("gather_prototype_max: empty batch")
+    score, image = full_pooled.max(dim=0)
+    # torch.max returns the first maximal row on CPU and CUDA for a 2-D reduction only by convention; make it explicit
+    is_max = full_pooled == score[None, :]
+    idx = torch.arange(full_pooled.shape[0], device=pooled.device)[:, None].expand_as(full_pooled)
+    image = torch.where(is_max, idx, torch.full_like(idx, full_pooled.shape[0])).min(dim=0).values
+    token = full_arg.gather(0, image[None, :])[0].long()
+    return score, image, token

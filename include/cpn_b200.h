@@ -114,6 +114,17 @@ int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const f
 int cpn_softmax_pool(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
                      float* partial, int B, int HW, int P, int chunks, void* stream);
 
+/* cpn_softmax_pool with, for max pooling, the patch token (h * W + w) of every chunk maximum: partial_arg
+ * [B,chunks,P] int32 (NULL = cpn_softmax_pool). cpn_pool_argmax_reduce folds the chunks into arg_out [B,P]: the
+ * location of each prototype's spatial maximum per image, lowest token on ties like torch.max -- what the reference's
+ * visualisation computes from the full map (util/vis_pipnet.py:209-274, 1095-1147) and what the multi-GPU
+ * per-prototype max gather of SURVEY section 8(e) exchanges. */
+int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode,
+                         float* map, float* partial, int* partial_arg, int B, int HW, int P, int chunks,
+                         void* stream);
+int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* partial_arg, int chunks, int* arg_out,
+                           int B, int P, void* stream);
+
 /* Chunk reduction, inference threshold (pipnet/pipnet.py:36) or round+clamp (pipnet/count_pipnet.py:90-97),
  * count encoding, and the non-negative classifier F.linear(x, relu(W), b) (pipnet/pipnet.py:70-71).
  * pooled_out [B,P] is the module's second return value; logits_out [B,K] the third. */

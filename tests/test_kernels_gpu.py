@@ -231,6 +231,43 @@ def test_softmax_pool_register_path(cuda_device, mode, P, HW, chunks):
         assert (partial.sum(1) - sm.sum(1)).abs().max().item() < 1e-4
 
 
+@pytest.mark.parametrize("with_map", [False, True])
+@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5), (16, 49, 2)])
+def test_softmax_pool_argmax(cuda_device, with_map, P, HW, chunks):
+    """Token of each prototype's spatial maximum (both softmax kernels), bit-exact incl. ties -> lowest token."""
+    g = torch.Generator().manual_seed(P + HW + 1)
+    B = 3
+    z = (torch.randn(B, HW, P, generator=g) * 3)
+    z[0, HW - 1] = z[0, 0]          # duplicated tokens: exact ties across warps and chunks
+    z[1, HW // 2] = z[1, HW // 2 - 1]
+    z[2, :, 0] = -200.0             # a prototype whose probability underflows to 0 everywhere -> token 0
+    z = z.to(cuda_device)
+    partial = torch.full((B, chunks, P), float("nan"), device=cuda_device)
+    parg = torch.full((B, chunks, P), -1, dtype=torch.int32, device=cuda_device)
+    arg = torch.full((B, P), -1, dtype=torch.int32, device=cuda_device)
+    pmap = torch.empty(B, P, HW, device=cuda_device) if with_map else None
+    ops.softmax_pool(z, partial, B, HW, P, chunks, mode=_lib.POOL_MAX, map_out=pmap, partial_arg=parg)
+    ops.pool_argmax_reduce(partial, parg, chunks, arg, B, P)
+    torch.cuda.synchronize()
+    # reference on the kernel's own probabilities where the map exists, else on torch's softmax away from near-ties
+    sm = pmap if with_map else torch.softmax(z, dim=2).permute(0, 2, 1)
+    ref_val, ref_arg = sm.max(dim=2)
+    is_max = sm == ref_val[:, :, None]
+    first = torch.where(is_max, torch.arange(HW, device=cuda_device)[None, None, :], HW).amin(2)
+    if with_map:
+        assert torch.equal(arg.long(), first)
+    else:
+        srt = sm.sort(dim=2).values
+        clear = (srt[:, :, -1] - srt[:, :, -2]) > 1e-5 * srt[:, :, -1].clamp_min(1e-30)
+        assert torch.equal(arg.long()[clear], first[clear])
+        # the planted exact ties must resolve to the lower token
+        picked = torch.softmax(z, dim=2).permute(0, 2, 1).gather(2, arg.long()[:, :, None])[:, :, 0]
+        assert (picked - ref_val).abs().max().item() < 1e-6
+        assert not (arg[0] == HW - 1).any() and not (arg[1] == HW // 2).any()
+    assert int(arg[2, 0]) == 0
+    assert (partial.amax(1) - ref_val).abs().max().item() < 1e-6
+
+
 def test_softmax_pool_gumbel_hard(cuda_device):
     g = torch.Generator().manual_seed(9)
     B, HW, P, chunks = 2, 64, 16, 2

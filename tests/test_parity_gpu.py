@@ -110,6 +110,45 @@ def test_fused_forward_matches_live_oracle_and_skips_map(cuda_device, name):
     assert np.array_equal(out.argmax(1), o_out.argmax(1).numpy())
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["cfg2_pipnet_convnext26_224", "pipnet_convnext13_addon32_bias", "pipnet_resnet18_64"])
+def test_prototype_argmax_without_map(cuda_device, name, precision):
+    """model.track_prototype_argmax: the patch of every prototype's maximum per image, produced by the pooling kernel
+    with the map not written, against the reference's golden arg-max (util/vis_pipnet.py:209-274 reads it off the
+    map). fp32: exact where the maximum is not a near-tie; bf16: the picked patch must score within the bf16-mode
+    tolerance of the reference maximum."""
+    case = cases.CASES[name]
+    g = dict(np.load(os.path.join(GOLDEN, name + ".npz")))
+    model = cases.build(case, my_pipnet, my_count).to(cuda_device)
+    model.cpn_precision = precision
+    x = cases.inputs(case).to(cuda_device)
+    with torch.no_grad():
+        model.materialize_proto_map = True
+        proto, pooled_m, _ = model(x, inference=case["inference"])
+        model.materialize_proto_map = False
+        model.track_prototype_argmax = True
+        none, pooled, _ = model(x, inference=case["inference"])
+    torch.cuda.synchronize()
+    assert none is None
+    am = model.cpn_prototype_argmax
+    hf, wf = model.cpn_patch_grid
+    assert tuple(am.shape) == tuple(g["map_argmax"].shape) and am.dtype == torch.int32
+    assert (hf, wf) == tuple(int(v) for v in g["map_shape"][2:])
+    flat = proto.reshape(proto.shape[0], proto.shape[1], -1)
+    # self-consistency with this library's own map: the token holds the maximum
+    picked = flat.gather(2, am.long()[:, :, None])[:, :, 0]
+    assert (picked - flat.amax(2)).abs().max().item() <= 1e-6
+    srt = np.sort(flat.cpu().numpy(), axis=2)
+    clear = (srt[:, :, -1] - srt[:, :, -2]) > 1e-3 * np.maximum(srt[:, :, -1], 1e-6)
+    if precision == "fp32":
+        assert np.array_equal(am.cpu().numpy()[clear], g["map_argmax"][clear])
+    else:
+        ref_at = np.take_along_axis(flat.cpu().numpy(), g["map_argmax"][:, :, None].astype(np.int64), axis=2)[:, :, 0]
+        scale = np.abs(g["map_max"]).max()
+        assert np.abs(ref_at - picked.cpu().numpy()).max() <= TOL["bf16"] * scale
+        assert (am.cpu().numpy() == g["map_argmax"])[clear].mean() > 0.9
+
+
 def test_backbone_standalone_nchw(cuda_device):
     """`net._net(x)` on its own returns NCHW features like the reference backbone."""
     case = cases.CASES["count_linear_softmax"]

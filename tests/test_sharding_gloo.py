@@ -48,3 +48,30 @@ def test_gather_two_ranks_gloo():
             ret = m.dict()
             mp.spawn(_worker, args=(2, _free_port(), batch, ret), nprocs=2, join=True)
             assert ret[0] and ret[1], dict(ret)
+
+
+def _worker_protomax(rank, world, port, batch, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(11)
+    feats = torch.randn(batch, 12, 3, 4, generator=g)
+    feats[batch - 1] = feats[0]  # the same image on two ranks: the tie must go to the lower image index
+    mine = sharding.my_shard(feats)
+    flat = torch.softmax(mine, dim=1).flatten(2)
+    pooled, arg = flat.max(dim=2)
+    score, image, token = sharding.gather_prototype_max(pooled, arg.int(), batch)
+    ref_flat = torch.softmax(feats, dim=1).flatten(2)  # [B, P, HW]
+    ref_pooled, ref_arg = ref_flat.max(dim=2)
+    ref_score = ref_pooled.max(dim=0).values
+    ref_image = torch.stack([(ref_pooled[:, p] == ref_score[p]).nonzero()[0, 0] for p in range(12)])
+    ref_token = ref_arg.gather(0, ref_image[None, :])[0]
+    ret[rank] = bool(torch.equal(score, ref_score) and torch.equal(image, ref_image) and torch.equal(token, ref_token))
+    dist.destroy_process_group()
+
+
+def test_prototype_max_gather_two_ranks_gloo():
+    for batch in (8, 5):
+        with mp.Manager() as m:
+            ret = m.dict()
+            mp.spawn(_worker_protomax, args=(2, _free_port(), batch, ret), nprocs=2, join=True)
+            assert ret[0] and ret[1], dict(ret)
