@@ -289,7 +289,8 @@ def roofline_report(plan, batch):
         kernels[name] = {"launches_per_step": n // passes, "ms_per_step": ms / passes, "share": ms / passes / total_ms,
                          "tflops": flops / ms / 1e9 if ms > 0 else None, "gbs": nbytes / ms / 1e6 if ms > 0 else None}
     dom = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
-    if kernels[dom]["tflops"] and dom.startswith("gemm"):
+    is_tensor = lambda k: k.startswith("gemm") or k.startswith("mlp_fused")  # tcgen05 kernels
+    if kernels[dom]["tflops"] and is_tensor(dom):
         roof = {"kernel": dom, "bound": "tensor", "achieved": kernels[dom]["tflops"], "peak": peaks["bf16_sustained"],
                 "unit": "TFLOP/s", "frac": kernels[dom]["tflops"] / peaks["bf16_sustained"], "traffic": None,
                 "peak_source": peaks["source"] + ", sustained figure (kernel timed inside the step)"}
@@ -303,10 +304,13 @@ def roofline_report(plan, batch):
                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": kernels[dwk]["gbs"] / peaks["hbm_gbs"],
                "note": "HBM by algorithmic bytes (4 B in + 2 B out per element); 49 fp32 FMAs per element make the "
                        "FMA pipe the practical bound (tflops in `kernels`, 74 TFLOP/s fp32 peak)"}
-    if "gemm_bf16" in kernels or "gemm_bf16x3" in kernels:
-        gk = "gemm_bf16" if "gemm_bf16" in kernels else "gemm_bf16x3"
-        tensor = {"kernel": gk, "bound": "tensor", "achieved": kernels[gk]["tflops"], "peak": peaks["bf16_sustained"],
-                  "unit": "TFLOP/s", "frac": kernels[gk]["tflops"] / peaks["bf16_sustained"]}
+    fam = [k for k in agg if is_tensor(k)]
+    if fam:
+        # all tcgen05 kernels of the step together (fused CNBlock MLPs + the remaining GEMMs): FLOPs / device time
+        f_ms = sum(agg[k][0] for k in fam)
+        f_tf = sum(agg[k][1] for k in fam) / f_ms / 1e9
+        tensor = {"kernel": "+".join(sorted(fam)), "bound": "tensor", "achieved": f_tf, "peak": peaks["bf16_sustained"],
+                  "unit": "TFLOP/s", "frac": f_tf / peaks["bf16_sustained"], "ms_per_step": f_ms / passes}
     return {"roofline": roof, "roofline_hbm_kernel": hbm, "roofline_tensor_kernel": tensor, "kernels": kernels,
             "step_tflops": FLOP_PER_IMAGE * batch / (total_ms * 1e-3) / 1e12}
 

@@ -12,7 +12,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libcpnb200.so")
 SOURCES = ["api.cu"]
-HEADERS = ["ptx.cuh", "gemm_tcgen05.cuh", "gemm_tma_epi.cuh", "gelu_fast.cuh", "convnext_kernels.cuh", "dwconv_stats.cuh", "dwconv_tma.cuh", "head_kernels.cuh", "layout_kernels.cuh",
+HEADERS = ["ptx.cuh", "gemm_tcgen05.cuh", "gemm_tma_epi.cuh", "gelu_fast.cuh", "convnext_kernels.cuh", "dwconv_stats.cuh", "mlp_fused.cuh", "dwconv_tma.cuh", "head_kernels.cuh", "layout_kernels.cuh",
            os.path.join("..", "..", "include", "cpn_b200.h")]
 
 NVCC_FLAGS = [

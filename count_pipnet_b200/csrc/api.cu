@@ -21,6 +21,7 @@
 #include "gemm_tma_epi.cuh"
 #include "head_kernels.cuh"
 #include "layout_kernels.cuh"
+#include "mlp_fused.cuh"
 
 namespace {
 
@@ -466,6 +467,51 @@ int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat1
 }
 }  // namespace
 
+namespace {
+struct MlpLaunch {
+    CUtensorMap tx, tw1, tw2;
+    cpn::MlpParams p;
+    int grid;
+};
+
+template <int C, int CG>
+int launch_mlp_inst(const MlpLaunch& g, cudaStream_t st) {
+    using S = cpn::MlpCfg<C, CG>;
+    auto kern = cpn::mlp_fused_kernel<C, CG>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        attr_done = true;
+    }
+    if (CG == 1) {
+        kern<<<g.grid, S::THREADS, S::TOTAL, st>>>(g.tx, g.tw1, g.tw2, g.p);
+    } else {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(g.grid);
+        cfg.blockDim = dim3(S::THREADS);
+        cfg.dynamicSmemBytes = S::TOTAL;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CPN_CUDA(cudaLaunchKernelEx(&cfg, kern, g.tx, g.tw1, g.tw2, g.p));
+    }
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int mlp_cg(int C) {
+    static const int env = [] { const char* e = getenv("CPN_MLP_CG"); return e == nullptr ? 0 : atoi(e); }();
+    if (C == 384) return 2;  // single CTAs have no room for the weight ring next to the 96 KB X tile
+    return env == 1 ? 1 : 2;
+}
+}  // namespace
+
 extern "C" {
 
 int cpn_version(void) { return 100; }
@@ -673,6 +719,80 @@ int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N
     set_info("gemm_bf16", 2.0 * mn * K, 2.0 * (static_cast<double>(M) * K + static_cast<double>(N) * K) + 2.0 * mn,
              "M=%d N=%d K=%d BN=%d cg=%d epi=ln_gelu_bf16", M, N, K, bn2, g.cg);
     return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
+}
+
+
+int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const void* w2, int M, int C, const float* stats,
+                  int nparts, const float* colsum, const float* bias1, const float* bias2, const float* scale, float eps,
+                  float* x, void* stream) {
+    if (M <= 0) return fail("cpn_mlp_fused: bad M=%d", M);
+    if (C != 96 && C != 192 && C != 384) return fail("cpn_mlp_fused: C must be 96, 192 or 384 (C=%d)", C);
+    if (nparts != C / 32) return fail("cpn_mlp_fused: nparts=%d, expected C/32=%d", nparts, C / 32);
+    if (y_bf16 == nullptr || w1g == nullptr || w2 == nullptr || stats == nullptr || colsum == nullptr ||
+        bias1 == nullptr || bias2 == nullptr || scale == nullptr || x == nullptr)
+        return fail("cpn_mlp_fused: missing operand");
+    if ((reinterpret_cast<uintptr_t>(x) & 15) != 0) return fail("cpn_mlp_fused: x not 16-byte aligned");
+    const int cg = mlp_cg(C);
+    const int n2 = C > 256 ? C / 2 : C;
+    MlpLaunch g;
+    memset(&g, 0, sizeof(g));
+    if (make_tmap(&g.tx, y_bf16, M, C, cpn::GEMM_BM) != 0) return -1;
+    if (make_tmap(&g.tw1, w1g, 4LL * C, C, 64 / cg) != 0) return -1;
+    if (make_tmap(&g.tw2, w2, C, 4 * C, n2 / cg) != 0) return -1;
+    g.p.M = M;
+    g.p.num_tiles = (M + cg * cpn::GEMM_BM - 1) / (cg * cpn::GEMM_BM);
+    g.p.stats = stats; g.p.nparts = nparts; g.p.inv_c = 1.0f / static_cast<float>(C); g.p.eps = eps;
+    g.p.colsum = colsum; g.p.bias1 = bias1; g.p.bias2 = bias2; g.p.scale = scale; g.p.x = x;
+    static const int mlp_dbg = [] { const char* e = getenv("CPN_MLP_DBG"); return e == nullptr ? 0 : atoi(e); }();
+    g.p.dbg = mlp_dbg;
+    const int slots = num_sms() / cg;
+    g.grid = cg * (g.p.num_tiles < slots ? g.p.num_tiles : slots);
+    const double mc = static_cast<double>(M) * C;
+    set_info("mlp_fused", 16.0 * mc * C, 2.0 * mc + 8.0 * mc + 16.0 * C * C, "M=%d C=%d cg=%d", M, C, cg);
+    static long long* ts_dev = nullptr;  // dev only: CPN_MLP_TS=1 prints a clock64 trace of CTA 0's first tile
+    static const bool want_ts = getenv("CPN_MLP_TS") != nullptr;
+    if (want_ts && plan == nullptr) {
+        if (ts_dev == nullptr) CPN_CUDA(cudaMalloc(&ts_dev, 512 * sizeof(long long)));
+        CPN_CUDA(cudaMemset(ts_dev, 0, 512 * sizeof(long long)));
+        g.p.ts = ts_dev;
+    }
+    auto run = [=](cudaStream_t st) -> int {
+        if (cg == 2) {
+            switch (C) {
+                case 96: return launch_mlp_inst<96, 2>(g, st);
+                case 192: return launch_mlp_inst<192, 2>(g, st);
+                default: return launch_mlp_inst<384, 2>(g, st);
+            }
+        }
+        return C == 96 ? launch_mlp_inst<96, 1>(g, st) : launch_mlp_inst<192, 1>(g, st);
+    };
+    if (g.p.ts != nullptr) {
+        if (run(static_cast<cudaStream_t>(stream)) != 0) return -1;
+        CPN_CUDA(cudaDeviceSynchronize());
+        static long long h[512];
+        CPN_CUDA(cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost));
+        long long t0 = h[0];
+        for (int j = 0; j < 512; ++j) if (h[j] != 0 && h[j] < t0) t0 = h[j];
+        fprintf(stderr, "# epilogue warp 4 (chunk: start, a1_full, tmem_ld, a1_empty arrive, h_empty, math+sts, fence, h_full arrive)\n");
+        for (int j = 0; j < C / 16 && j < 32; ++j) {
+            fprintf(stderr, "E %2d:", j);
+            for (int k = 0; k < 8; ++k) fprintf(stderr, " %7lld", h[j * 8 + k] - t0);
+            fprintf(stderr, "\n");
+        }
+        fprintf(stderr, "# tiles of CTA 0 (chunk loop start, end, acc2 ready, final epilogue end)\n");
+        for (int t = 0; t < 8; ++t)
+            if (h[480 + 4 * t] != 0)
+                fprintf(stderr, "T %d: %7lld %7lld %7lld %7lld\n", t, h[480 + 4 * t] - h[480], h[481 + 4 * t] - h[480],
+                        h[482 + 4 * t] - h[480], h[483 + 4 * t] - h[480]);
+        fprintf(stderr, "# MMA thread (step: G1 start, w_full, a1_empty | G2 start, w_full, h_full)\n");
+        for (int j = 0; j <= C / 16 && j < 32; ++j) {
+            fprintf(stderr, "M %2d:", j);
+            for (int k = 0; k < 6; ++k) fprintf(stderr, " %7lld", h[256 + j * 8 + k] ? h[256 + j * 8 + k] - t0 : 0);
+            fprintf(stderr, "\n");
+        }
+        return 0;
+    }
+    return submit(plan, stream, run);
 }
 
 int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const float* ln_b, void* out_hi, void* out_lo,

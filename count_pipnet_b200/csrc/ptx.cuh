@@ -121,6 +121,16 @@ __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---------------------------------------------------------------- cp.async (LDGSTS)
+__device__ __forceinline__ void cp_async4(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_holder)),
@@ -202,12 +212,15 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
         : "memory");
 }
 // Arrive on the mbarrier at the same offset in the leader CTA (rank 0 of the pair); usable from either CTA.
+// Default semantics (release at CTA scope): the cluster-scope form costs a MEMBAR.ALL.GPU + ERRBAR per arrive, and
+// what the waiter consumes here (TMEM reads ordered by tcgen05.wait::ld, shared-memory writes already published to
+// the async proxy by fence.proxy.async) does not need it.
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
     asm volatile(
         "{\n\t"
         ".reg .b32 ra;\n\t"
         "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t"
         "}" ::"r"(smem_u32(bar))
         : "memory");
 }
@@ -241,6 +254,68 @@ __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
             smem_u32(bar)),
         "h"(static_cast<uint16_t>(3))
         : "memory");
+}
+
+// ---------------------------------------------------------------- warp-uniform issue (whole warp runs the loop)
+// One lane of the (converged) warp gets true. Keeping the MMA loop warp-uniform and predicating only the tcgen05
+// instructions lets the compiler build the descriptors in uniform registers instead of moving them there per MMA.
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred;
+}
+template <int CG>
+__device__ __forceinline__ void umma_bf16_if(uint32_t issue, uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                             uint32_t idesc, uint32_t accumulate) {
+    if (CG == 2) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p, q;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "setp.ne.b32 q, %5, 0;\n\t"
+            "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+            "}" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p, q;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "setp.ne.b32 q, %5, 0;\n\t"
+            "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+            "}" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
+            : "memory");
+    }
+}
+template <int CG>
+__device__ __forceinline__ void umma_commit_if(uint32_t issue, uint64_t* bar) {
+    if (CG == 2) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred q;\n\t"
+            "setp.ne.b32 q, %2, 0;\n\t"
+            "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t"
+            "}" ::"r"(smem_u32(bar)),
+            "h"(static_cast<uint16_t>(3)), "r"(issue)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred q;\n\t"
+            "setp.ne.b32 q, %1, 0;\n\t"
+            "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+            "}" ::"r"(smem_u32(bar)),
+            "r"(issue)
+            : "memory");
+    }
 }
 
 // ---------------------------------------------------------------- descriptors

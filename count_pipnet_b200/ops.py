@@ -105,6 +105,13 @@ def gemm_ln_gelu(a, bw, M, N, K, stats, nparts, colsum, bias, out_bf16, eps=1e-6
               float(eps), ptr(out_bf16), _stream())
 
 
+def mlp_fused(y_bf16, w1g, w2, M, C, stats, colsum, bias1, bias2, scale, x, eps=1e-6, plan=None):
+    """x += scale * fc2(gelu(fc1(LN(y)))) in one kernel: see cpn_mlp_fused in include/cpn_b200.h."""
+    _need_cuda(y_bf16, w1g, w2, stats, colsum, bias1, bias2, scale, x)
+    _lib.call("cpn_mlp_fused", _ph(plan), ptr(y_bf16), ptr(w1g), ptr(w2), M, C, ptr(stats), C // 32, ptr(colsum),
+              ptr(bias1), ptr(bias2), ptr(scale), float(eps), ptr(x), _stream())
+
+
 def ln_im2col2(x, ln_w, ln_b, out_hi, out_lo=None, stride=2, eps=1e-6, plan=None):
     """x [B,H,W,C] fp32 -> out [B*Ho*Wo, 4C] bf16."""
     _need_cuda(x, ln_w, ln_b, out_hi, out_lo)

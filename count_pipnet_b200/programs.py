@@ -19,6 +19,8 @@ from .features import resnet_features as rsn
 # Working-set target of one image chunk of a stage (bf16 mode); 0 = whole batch at once. Measured on B200 (B=64, cfg2):
 # chunking for L2 residency LOSES (6.6 ms at 96 MB chunks vs 4.9 ms unchunked) - the smaller GEMMs and depthwise convs
 # lose more to wave quantisation than the HBM round trips cost - so it is off unless CPN_L2_CHUNK_MB is set.
+# CPN_FUSED_MLP=0 falls back to the two-GEMM MLP (fc1 + LN/GELU epilogue, fc2 + scale/residual epilogue)
+FUSED_MLP = os.environ.get("CPN_FUSED_MLP", "1") != "0"
 L2_CHUNK_BYTES = float(os.environ.get("CPN_L2_CHUNK_MB", "0")) * 2 ** 20 or 1e18
 
 
@@ -179,6 +181,12 @@ class ConvNeXtProgram:
                 blk = s[1]
                 dw, ln, fc2 = blk.block[0], blk.block[2], blk.block[5]
                 ops.dwconv7_stats(res4[b0:b1], pk["w49"], dw.bias.detach(), a_hi[t0:t1], stats[t0:t1], plan=plan)
+                if FUSED_MLP and C in (96, 192, 384):
+                    # fc1 -> GELU -> fc2 -> layer scale -> residual in one kernel, hidden activations stay on the SM
+                    ops.mlp_fused(a_hi[t0:t1], pk["w1g"], pk["w2"], t1 - t0, C, stats[t0:t1], pk["w1g_sum"], pk["b1f"],
+                                  fc2.bias.detach(), blk.layer_scale.detach().view(C), res2[t0:t1], eps=ln.eps,
+                                  plan=plan)
+                    continue
                 ops.gemm_ln_gelu(a_hi[t0:t1], pk["w1g"], t1 - t0, 4 * C, C, stats[t0:t1], C // 32, pk["w1g_sum"],
                                  pk["b1f"], h_hi[t0:t1], eps=ln.eps, plan=plan)
                 ops.gemm_bf16(h_hi[t0:t1], pk["w2"], t1 - t0, C, 4 * C, bias=fc2.bias.detach(),

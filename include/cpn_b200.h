@@ -85,6 +85,16 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
 int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N, int K, const float* stats,
                      int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream);
 
+/* Whole CNBlock MLP in one kernel (bf16 mode; torchvision convnext.py:53-57, 64-66):
+ *   x[M,C] += scale * (gelu(rstd_m * (y * w1g^T - mean_m * colsum) + bias1) * w2^T + bias2)
+ * y [M,C] bf16 = un-normalised depthwise-conv output with its per-token partial sums stats [M, C/32, 2] (both from
+ * cpn_dwconv7_stats), w1g [4C,C] bf16 = W1 * gamma, colsum [4C] its row sums, bias1 [4C] = b1 + W1 * beta,
+ * w2 [C,4C] bf16, bias2 / scale [C]; x is the fp32 residual stream, updated in place. The 4C-wide hidden activations
+ * stay in shared / tensor memory. C in {96, 192, 384}. */
+int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const void* w2, int M, int C, const float* stats,
+                  int nparts, const float* colsum, const float* bias1, const float* bias2, const float* scale, float eps,
+                  float* x, void* stream);
+
 /* LayerNorm2d(C) then the im2col rows of Conv2d(C,C',k=2,stride) -- torchvision/models/convnext.py:146-150 with
  * the stride surgery of features/convnext_features.py:5-15.
  * x [B,H,W,C] fp32; out [B*Ho*Wo, 4*C] bf16 with column (kh*2+kw)*C + c, Ho = (H-2)/stride+1. */

@@ -176,6 +176,68 @@ def test_gemm_ln_gelu(cuda_device, M, C):
     assert err < 0.05 * max(1.0, ref.abs().max().item()) * 0.5, err
 
 
+def _mlp_operands(M, C, device, seed):
+    g = torch.Generator().manual_seed(seed)
+    N = 4 * C
+    y = (torch.randn(M, C, generator=g) * 1.5 + 0.7).to(device).to(torch.bfloat16)
+    w1 = (torch.randn(N, C, generator=g) / C ** 0.5).to(device)
+    b1 = torch.randn(N, generator=g).to(device)
+    gamma = (torch.rand(C, generator=g) + 0.5).to(device)
+    beta = torch.randn(C, generator=g).to(device)
+    w2 = (torch.randn(C, N, generator=g) / N ** 0.5).to(device)
+    b2 = torch.randn(C, generator=g).to(device)
+    scale = (torch.rand(C, generator=g) + 0.25).to(device)
+    x = torch.randn(M, C, generator=g).to(device)
+    yf = y.float().reshape(M, C // 32, 32)
+    stats = torch.stack([yf.sum(-1), (yf * yf).sum(-1)], dim=-1).contiguous()
+    w1g = (w1 * gamma[None, :]).to(torch.bfloat16).contiguous()
+    colsum = w1g.float().sum(1).contiguous()
+    b1f = (b1 + w1 @ beta).contiguous()
+    return dict(y=y, w1=w1, b1=b1, gamma=gamma, beta=beta, w2=w2, b2=b2, scale=scale, x=x, stats=stats, w1g=w1g,
+                colsum=colsum, b1f=b1f, w2b=w2.to(torch.bfloat16).contiguous())
+
+
+@pytest.mark.parametrize("cg", ["1", "2"])
+@pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (128, 96), (129, 192), (46656, 384), (50176, 192)])
+def test_mlp_fused(cuda_device, M, C, cg, monkeypatch):
+    """One-kernel CNBlock MLP against (a) the two-GEMM path of this library (same arithmetic: bf16 hidden activations,
+    fp32 accumulation) and (b) torch fp32. Several tiles per CTA at the large sizes; ragged last tiles."""
+    import subprocess, sys, os, json
+    # CPN_MLP_CG is read once per process: run the comparison in a child so that both settings are covered
+    code = f"""
+import sys, json, torch
+sys.path.insert(0, {os.path.dirname(os.path.abspath(__file__))!r})
+import torch.nn.functional as F
+from count_pipnet_b200 import ops
+from test_kernels_gpu import _mlp_operands
+M, C = {M}, {C}
+d = torch.device('cuda:0')
+o = _mlp_operands(M, C, d, C + M)
+x1 = o['x'].clone()
+ops.mlp_fused(o['y'], o['w1g'], o['w2b'], M, C, o['stats'], o['colsum'], o['b1f'], o['b2'], o['scale'], x1)
+x1b = o['x'].clone()
+ops.mlp_fused(o['y'], o['w1g'], o['w2b'], M, C, o['stats'], o['colsum'], o['b1f'], o['b2'], o['scale'], x1b)
+h = torch.empty(M, 4 * C, device=d, dtype=torch.bfloat16)
+ops.gemm_ln_gelu(o['y'], o['w1g'], M, 4 * C, C, o['stats'], C // 32, o['colsum'], o['b1f'], h)
+x2 = o['x'].clone()
+ops.gemm_bf16(h, o['w2b'], M, C, 4 * C, bias=o['b2'], scale=o['scale'], res_f32=x2, out_f32=x2)
+ref = o['x'] + o['scale'] * F.linear(F.gelu(F.linear(F.layer_norm(o['y'].float(), (C,), o['gamma'], o['beta'], 1e-6),
+                                                         o['w1'], o['b1'])), o['w2'], o['b2'])
+torch.cuda.synchronize()
+print(json.dumps(dict(vs_two_gemm=(x1 - x2).abs().max().item(), vs_torch=(x1 - ref).abs().max().item(),
+                      two_gemm_vs_torch=(x2 - ref).abs().max().item(), repeat=bool(torch.equal(x1, x1b)),
+                      scale=ref.abs().max().item())))
+"""
+    env = dict(os.environ, CPN_MLP_CG=cg, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    print(res)
+    assert res["repeat"]
+    assert res["vs_two_gemm"] <= 2e-3 * max(1.0, res["scale"]), res
+    assert res["vs_torch"] <= max(2.0 * res["two_gemm_vs_torch"], 1e-2 * max(1.0, res["scale"])), res
+
+
 @pytest.mark.parametrize("stride,H,W,C", [(2, 16, 16, 96), (1, 14, 14, 192), (1, 9, 11, 384)])
 def test_ln_im2col2(cuda_device, stride, H, W, C):
     g = torch.Generator().manual_seed(C)

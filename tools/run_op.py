@@ -63,6 +63,21 @@ def main():
             fn = lambda: ops.gemm_bf16(A, Wt, a.M, a.N, a.K, bias=bias, out_bf16=out, act=a.act)
             nbytes = A.numel() * 2 + Wt.numel() * 2 + out.numel() * 2
         flops = 2.0 * a.M * a.N * a.K
+    elif a.op == "mlp":
+        C = a.C
+        y = (torch.randn(a.M, C, generator=g)).to(dev).to(torch.bfloat16)
+        w1g = (torch.randn(4 * C, C, generator=g) / C ** 0.5).to(dev).to(torch.bfloat16)
+        w2 = (torch.randn(C, 4 * C, generator=g) / (4 * C) ** 0.5).to(dev).to(torch.bfloat16)
+        b1 = torch.randn(4 * C, generator=g).to(dev)
+        b2 = torch.randn(C, generator=g).to(dev)
+        scale = (torch.rand(C, generator=g) * 0.01).to(dev)
+        colsum = w1g.float().sum(1).contiguous()
+        yf = y.float().reshape(a.M, C // 32, 32)
+        stats = torch.stack([yf.sum(-1), (yf * yf).sum(-1)], dim=-1).contiguous()
+        x = torch.randn(a.M, C, generator=g).to(dev)
+        fn = lambda: ops.mlp_fused(y, w1g, w2, a.M, C, stats, colsum, b1, b2, scale, x)
+        nbytes = y.numel() * 2 + x.numel() * 8 + w1g.numel() * 4
+        flops = 16.0 * a.M * C * C
     else:
         raise SystemExit("unknown op")
     for _ in range(2):
