@@ -8,7 +8,7 @@ import threading
 
 _LIB = None
 _LOCK = threading.Lock()
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libcpnb200.so")
+LIB_PATH = os.environ.get("CPN_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libcpnb200.so")  # env: A/B builds (dev)
 
 _vp, _i, _f, _ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
 

@@ -743,6 +743,11 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
     g.p.num_tiles = (M + cg * cpn::GEMM_BM - 1) / (cg * cpn::GEMM_BM);
     g.p.stats = stats; g.p.nparts = nparts; g.p.inv_c = 1.0f / static_cast<float>(C); g.p.eps = eps;
     g.p.colsum = colsum; g.p.bias1 = bias1; g.p.bias2 = bias2; g.p.scale = scale; g.p.x = x;
+    // Groups that run one tile less than the others start half a tile late (estimated from the chunk count): the
+    // final epilogues of all CTAs otherwise hit HBM/L2 in the same few microseconds (profiles/r01_mlp_fused.md).
+    static const int stagger_pct = [] { const char* e = getenv("CPN_MLP_STAGGER"); return e == nullptr ? 50 : atoi(e); }();
+    const int tile_cycles = C == 384 ? 75000 : C == 192 ? 32000 : 15500;  // measured, profiles/r01_mlp_fused.md
+    g.p.stagger = tile_cycles / 100 * stagger_pct;  // negative percentage: delays spread over 0.5 .. 1.44 of it
     static const int mlp_dbg = [] { const char* e = getenv("CPN_MLP_DBG"); return e == nullptr ? 0 : atoi(e); }();
     g.p.dbg = mlp_dbg;
     const int slots = num_sms() / cg;

@@ -31,6 +31,7 @@ struct MlpParams {
     const float* scale;   // [C] layer_scale
     float* x;             // [M, C] fp32 residual stream, updated in place
     long long* ts;        // dev only (CPN_MLP_TS): clock64 trace of CTA 0's first tile, [2][32][8]
+    int stagger;          // cycles by which CTA groups with one tile less than the others start late (see api.cu)
     int dbg;              // timing experiments (CPN_MLP_DBG): 1 = E1 skips its math, 2 = no MMAs, 4 = no weight loads
 };
 
@@ -143,6 +144,13 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 if (CG == 2) ptx::tma_load_2d_2sm(dst, m, c0, c1, bar);
                 else ptx::tma_load_2d(dst, m, c0, c1, bar);
             };
+            if (p.stagger != 0 && tile0 + ((p.num_tiles - 1) / tile_step) * tile_step >= p.num_tiles) {
+                // this group has one tile less than the longest-running ones: starting late costs nothing and takes
+                // its residual read-modify-write bursts (final epilogue) out of phase with theirs
+                const long long t0 = clock64();
+                const long long d = p.stagger >= 0 ? p.stagger : (-p.stagger) / 2 + ((-p.stagger) * ((tile0 * 5) & 15)) / 16;
+                while (clock64() - t0 < d) {}
+            }
             for (int tile = tile0; tile < p.num_tiles; tile += tile_step, ++it) {
                 const int m0 = (tile * CG + static_cast<int>(rank)) * GEMM_BM;
                 ptx::mbar_wait(x_empty, (it & 1) ^ 1);  // the last G1 of the previous tile has read X
