@@ -273,6 +273,13 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch from an `ncu --set full` capture (not measured live)
+NCU_TRAFFIC = {
+    "mlp_fused": {"bytes": 137.6e6, "note": "stage-3 launch (M=46656, C=384), profiles/r01_mlp_fused.md: 114.5 MB read "
+                  "+ 23.1 MB written by kernel end; algorithmic 112 MB in + 72 MB out (output still dirty in L2)"},
+}
+
+
 def roofline_report(plan, batch):
     """Per-kernel device times from an event-separated replay of the recorded step (3 passes, averaged), and the
     roofline of the dominant kernel family (the tcgen05 GEMM) from its algorithmic FLOPs."""
@@ -292,7 +299,8 @@ def roofline_report(plan, batch):
     is_tensor = lambda k: k.startswith("gemm") or k.startswith("mlp_fused")  # tcgen05 kernels
     if kernels[dom]["tflops"] and is_tensor(dom):
         roof = {"kernel": dom, "bound": "tensor", "achieved": kernels[dom]["tflops"], "peak": peaks["bf16_sustained"],
-                "unit": "TFLOP/s", "frac": kernels[dom]["tflops"] / peaks["bf16_sustained"], "traffic": None,
+                "unit": "TFLOP/s", "frac": kernels[dom]["tflops"] / peaks["bf16_sustained"],
+                "traffic": NCU_TRAFFIC.get(dom, {}).get("bytes"), "traffic_note": NCU_TRAFFIC.get(dom, {}).get("note"),
                 "peak_source": peaks["source"] + ", sustained figure (kernel timed inside the step)"}
     else:
         roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",

@@ -156,8 +156,10 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ------------------------------------------------------------ MMA issuer (single thread)
-        if (lane == 0 && rank == 0) {
+        // ------------------------------------------------------------ MMA issuer: the whole warp walks the loop
+        // (uniform control flow, so the descriptors live in uniform registers) and one elected lane issues
+        if (rank == 0) {
+            const uint32_t el = ptx::elect_one();
             constexpr uint32_t idesc = ptx::make_idesc_bf16(GEMM_BM * CG, BN);
             int stage = 0;
             uint32_t phase = 0;
@@ -176,16 +178,10 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
                     for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k) {
                         if (p.dbg & 2) continue;
-                        if (CG == 2) ptx::umma_bf16_2sm(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                        else ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        ptx::umma_bf16_if<CG>(el, tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                     }
-                    if (CG == 2) {
-                        ptx::umma_commit_2sm(&empty_bar[stage]);  // frees the stage in both CTAs
-                        if (kb == p.num_k_blocks - 1) ptx::umma_commit_2sm(&tmem_full_bar[as]);
-                    } else {
-                        ptx::umma_commit(&empty_bar[stage]);
-                        if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[as]);
-                    }
+                    ptx::umma_commit_if<CG>(el, &empty_bar[stage]);  // frees the stage (in both CTAs of a pair)
+                    if (kb == p.num_k_blocks - 1) ptx::umma_commit_if<CG>(el, &tmem_full_bar[as]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
