@@ -997,6 +997,21 @@ int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* part
     });
 }
 
+int cpn_topk_update(cpn_plan* plan, const float* pooled, const int* argmax, int B, int P, int k, long long image_base,
+                    float* top_val, long long* top_img, int* top_tok, int* top_cnt, void* stream) {
+    if (pooled == nullptr || argmax == nullptr || top_val == nullptr || top_img == nullptr || top_tok == nullptr ||
+        top_cnt == nullptr)
+        return fail("cpn_topk_update: missing operand");
+    if (B <= 0 || P <= 0 || k <= 0) return fail("cpn_topk_update: bad shape B=%d P=%d k=%d", B, P, k);
+    set_info("topk_update", 0.0, 8.0 * B * P + 16.0 * k * P);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::topk_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(pooled, argmax, B, P, k, image_base, top_val, top_img,
+                                                                 top_tok, top_cnt);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
 int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, int inference, int use_ste,
                   int max_count, int encoding, const float* enc_w0, const float* enc_w1, const float* enc_w2,
                   const float* cls_w, const float* cls_b, float* pooled_out, float* logits_out, int B, int P, int D,

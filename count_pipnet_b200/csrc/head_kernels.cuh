@@ -141,6 +141,34 @@ __global__ void pool_argmax_reduce_kernel(const float* __restrict__ partial, con
     arg_out[static_cast<size_t>(b) * P + p] = ai == 0x7fffffff ? 0 : ai;
 }
 
+// Running top-k images per prototype (util/vis_pipnet.py:226-271: an image enters prototype p's list while the list is
+// shorter than k or when its score is strictly greater than the last entry's; the list stays sorted by descending
+// score, equal scores in arrival order). One thread per prototype walks the batch in image order, so the result is
+// what the reference's one-image-at-a-time loop builds. Lists are [k, P] (coalesced across the threads of a warp).
+__global__ void topk_update_kernel(const float* __restrict__ pooled, const int* __restrict__ argmax, int B, int P, int k,
+                                   long long image_base, float* __restrict__ val, long long* __restrict__ img,
+                                   int* __restrict__ tok, int* __restrict__ cnt) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    int n = cnt[p];
+    for (int b = 0; b < B; ++b) {
+        const float s = pooled[static_cast<size_t>(b) * P + p];
+        if (n == k && !(s > val[static_cast<size_t>(k - 1) * P + p])) continue;
+        int i = n < k ? n : k - 1;  // slot that opens up (append, or the dropped last entry)
+        while (i > 0 && val[static_cast<size_t>(i - 1) * P + p] < s) {
+            val[static_cast<size_t>(i) * P + p] = val[static_cast<size_t>(i - 1) * P + p];
+            img[static_cast<size_t>(i) * P + p] = img[static_cast<size_t>(i - 1) * P + p];
+            tok[static_cast<size_t>(i) * P + p] = tok[static_cast<size_t>(i - 1) * P + p];
+            --i;
+        }
+        val[static_cast<size_t>(i) * P + p] = s;
+        img[static_cast<size_t>(i) * P + p] = image_base + b;
+        tok[static_cast<size_t>(i) * P + p] = argmax[static_cast<size_t>(b) * P + p];
+        if (n < k) ++n;
+    }
+    cnt[p] = n;
+}
+
 // Register-resident variant for the common case (plain softmax, no map, P a multiple of 128 up to 1024): each lane
 // owns the same 4*NV prototypes of every token (NV float4 per lane, loaded once, coalesced 512 B per warp and
 // instruction), so the row max / sum are two warp reductions, the probabilities never leave registers and the running

@@ -186,3 +186,11 @@ def maxpool3s2(x, B, H, W, Cc, out_f32=None, out_hi=None, out_lo=None, plan=None
 def subsample2_bf16(x, out, B, H, W, Cc, plan=None):
     _need_cuda(x, out)
     _lib.call("cpn_subsample2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())
+
+
+def topk_update(pooled, argmax, image_base, top_val, top_img, top_tok, top_cnt, plan=None):
+    """Merges a batch into the running per-prototype top-k lists [k, P]: see cpn_topk_update in include/cpn_b200.h."""
+    _need_cuda(pooled, argmax, top_val, top_img, top_tok, top_cnt)
+    B, P = pooled.shape
+    _lib.call("cpn_topk_update", _ph(plan), ptr(pooled), ptr(argmax), B, P, top_val.shape[0], int(image_base),
+              ptr(top_val), ptr(top_img), ptr(top_tok), ptr(top_cnt), _stream())

@@ -135,6 +135,15 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
 int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* partial_arg, int chunks, int* arg_out,
                            int B, int P, void* stream);
 
+/* Running top-k images per prototype over a stream of batches (the search loop of util/vis_pipnet.py:209-271, which
+ * runs one image per forward on the host): merges pooled [B,P] / argmax [B,P] (cpn_pool_argmax_reduce) of images
+ * image_base .. image_base + B - 1 into top_val / top_img / top_tok [k,P] and top_cnt [P] (zero-initialised by the
+ * caller before the first batch). An image enters a list shorter than k, or when its score is strictly greater than
+ * the last entry's; lists stay sorted by descending score, equal scores in arrival order -- entry for entry what the
+ * reference's loop keeps. */
+int cpn_topk_update(cpn_plan* plan, const float* pooled, const int* argmax, int B, int P, int k, long long image_base,
+                    float* top_val, long long* top_img, int* top_tok, int* top_cnt, void* stream);
+
 /* Chunk reduction, inference threshold (pipnet/pipnet.py:36) or round+clamp (pipnet/count_pipnet.py:90-97),
  * count encoding, and the non-negative classifier F.linear(x, relu(W), b) (pipnet/pipnet.py:70-71).
  * pooled_out [B,P] is the module's second return value; logits_out [B,K] the third. */
