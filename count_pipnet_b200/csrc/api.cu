@@ -335,7 +335,9 @@ int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, 
     const long long pair_tiles = static_cast<long long>((M + 2 * cpn::GEMM_BM - 1) / (2 * cpn::GEMM_BM)) * (N / bn);
     // Measured (profiles/r01_gemm_pairs.md): pairs help the K-heavy fp32-output GEMMs (fc2: +4 % at K=1536, +14 % at
     // K=3072) and cost a few percent on the epilogue-heavy bf16-output ones (fc1), so only the former use them.
-    const bool wanted = !cpn::epi_out_bf16(epi) || allow >= 2;  // CPN_GEMM_2SM=2 forces pairs everywhere (tests)
+    // Since the pair's epilogue arrives no longer carry a GPU-scope fence (ptx::mbar_arrive_leader) pairs also gain
+    // 2 % on fc1 at K = 768 (0.1970 vs 0.2009 ms); at K = 384 the difference is within noise.
+    const bool wanted = !cpn::epi_out_bf16(epi) || K >= 768 || allow >= 2;  // CPN_GEMM_2SM=2: pairs everywhere (tests)
     g.cg = (allow != 0 && wanted && (bn == 256 || bn == 192 || bn == 128) && (pair_tiles >= pairs || allow == 2)) ? 2 : 1;
     if (make_tmap(&g.tb, Bw, N, K, bn / g.cg) != 0) return -1;
     g.p.num_m_blocks = (M + g.cg * cpn::GEMM_BM - 1) / (g.cg * cpn::GEMM_BM);
