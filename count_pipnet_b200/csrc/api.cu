@@ -1039,12 +1039,17 @@ int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, in
     }
     const size_t smem = (static_cast<size_t>(P) + 2 * static_cast<size_t>(D)) * sizeof(float);
     if (smem > 200 * 1024) return fail("cpn_head_tail: P=%d D=%d too large", P, D);
+    // class slices per image: enough CTAs to fill the GPU when the batch alone does not (64 images on 148 SMs)
+    int ks = (4 * num_sms() + B - 1) / B;
+    ks = ks < 1 ? 1 : (ks > 8 ? 8 : ks);
+    if (ks > (K + 7) / 8) ks = (K + 7) / 8;  // at least one class per warp
+    if (D > 4096) ks = 1;                    // dense count encodings are not worth repeating
     set_info("head_tail", 2.0 * B * D * K, 4.0 * B * (1.0 * chunks * P + 1.0 * D * K));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(smem)));
-        cpn::head_tail_kernel<<<B, 256, smem, st>>>(tp);
+        cpn::head_tail_kernel<<<dim3(B, ks), 256, smem, st>>>(tp);
         CPN_CUDA(cudaGetLastError());
         return 0;
     });

@@ -301,7 +301,8 @@ struct TailParams {
     int P, D, K;
 };
 
-// One CTA per image. Shared memory: pooled[P] | inter[D] | tmp[D]
+// gridDim.x = images, gridDim.y = class slices: every CTA of an image repeats the (cheap) chunk reduction and encoding
+// and computes the classes k = blockIdx.y, blockIdx.y + gridDim.y, ... Shared memory: pooled[P] | inter[D] | tmp[D]
 __global__ void __launch_bounds__(256)
 head_tail_kernel(const TailParams p) {
     extern __shared__ float s_buf[];
@@ -331,7 +332,7 @@ head_tail_kernel(const TailParams p) {
             ret = p.inference ? a : counts;
         }
         s_pooled[i] = a;
-        p.pooled_out[static_cast<size_t>(b) * p.P + i] = ret;
+        if (blockIdx.y == 0) p.pooled_out[static_cast<size_t>(b) * p.P + i] = ret;
     }
     __syncthreads();
 
@@ -380,7 +381,7 @@ head_tail_kernel(const TailParams p) {
     __syncthreads();
 
     // non-negative classifier: logits[k] = sum_d relu(W[k,d]) * inter[d] + bias[k]
-    for (int k = warp; k < p.K; k += wpb) {
+    for (int k = blockIdx.y + warp * gridDim.y; k < p.K; k += wpb * gridDim.y) {
         const float* wr = p.cls_w + static_cast<size_t>(k) * p.D;
         float a = 0.f;
         for (int d = lane; d < p.D; d += 32) a = fmaf(s_inter[d], fmaxf(__ldg(wr + d), 0.f), a);

@@ -5,6 +5,7 @@ util/interpret_idg.py:171-172, notebooks/main_interp.py:167-168)."""
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -18,6 +19,8 @@ from .programs import ConvNeXtProgram, Emit
 from .programs_resnet import ResNetProgram
 
 NUM_SMS = 148
+# CTAs of the softmax/pool kernel per SM (each takes a chunk of one image's tokens); env for measurement only
+POOL_CHUNK_FACTOR = float(os.environ.get("CPN_POOL_CHUNKS", "3"))
 
 
 def _make_program(backbone: nn.Module):
@@ -101,7 +104,7 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
     else:
         P, z = C, feat
     noise = em.buf("gumbel", (B, P, Hf, Wf), torch.float32) if gumbel else None
-    chunks = max(1, min(max(HW // 8, 1), math.ceil(2 * NUM_SMS / B)))
+    chunks = max(1, min(max(HW // 8, 1), math.ceil(POOL_CHUNK_FACTOR * NUM_SMS / B)))
     partial = em.buf("partial", (B, chunks, P), torch.float32)
     pmap = em.buf("map", (B, P, Hf, Wf), torch.float32) if want_map else None
     mode = _lib.POOL_SUM if is_count else _lib.POOL_MAX
