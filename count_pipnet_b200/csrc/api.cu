@@ -820,6 +820,19 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
         long long want = (ntok + 15) / 16;
         const long long cap = 8LL * num_sms();
         const int pgrid = static_cast<int>(want < cap ? want : cap);
+        static const bool v3 = getenv("CPN_LNIM_V2") == nullptr;
+        if (v3 && (C == 96 || C == 192 || C == 384)) {
+            const int tpw = 32 / (C / 12);
+            long long want3 = (ntok + 16 * tpw - 1) / (16 * tpw);  // 8 warps x 2 passes x tpw tokens per CTA
+            const int pgrid3 = static_cast<int>(want3 < cap ? want3 : cap);
+            return submit(plan, stream, [=](cudaStream_t st) -> int {
+                if (C == 96) cpn::ln_im2col3_bf16_kernel<8><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
+                else if (C == 192) cpn::ln_im2col3_bf16_kernel<16><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
+                else cpn::ln_im2col3_bf16_kernel<32><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
+                CPN_CUDA(cudaGetLastError());
+                return 0;
+            });
+        }
         return submit(plan, stream, [=](cudaStream_t st) -> int {
             switch (nv) {
                 case 1: cpn::ln_im2col2_bf16_kernel<1><<<pgrid, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, C, stride, Ho, Wo, eps); break;

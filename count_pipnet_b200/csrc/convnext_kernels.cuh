@@ -480,4 +480,84 @@ ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
     }
 }
 
+// C = 12 * LPT channels (96 / 192 / 384 = the three ConvNeXt-tiny downsample inputs): LPT lanes share a token, three
+// float4 per lane, so a warp normalises 32 / LPT tokens per pass with log2(LPT) shuffle levels and every lane busy
+// (the generic kernel above leaves 8 of 32 lanes idle at C = 96 and spends most of its time on per-token index math).
+// Two passes are in flight per warp; warps stride over the token list (persistent grid).
+template <int LPT>
+__global__ void __launch_bounds__(256)
+ln_im2col3_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                       __nv_bfloat16* __restrict__ out, int B, int H, int W, int stride, int Ho, int Wo, float eps) {
+    constexpr int TPW = 32 / LPT;  // tokens per warp and pass
+    constexpr int C = 12 * LPT;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sub = lane / LPT, l = lane % LPT;
+    const int ntok = B * H * W;
+    const int nwarps = gridDim.x * (blockDim.x >> 5);
+    float4 gw[3], gb[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        gw[i] = __ldg(reinterpret_cast<const float4*>(ln_w) + l + LPT * i);
+        gb[i] = __ldg(reinterpret_cast<const float4*>(ln_b) + l + LPT * i);
+    }
+    const float inv_c = 1.0f / static_cast<float>(C);
+    for (int g = (blockIdx.x * (blockDim.x >> 5) + warp) * 2; g * TPW < ntok; g += 2 * nwarps) {
+        float4 v[2][3];
+        int tok[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            tok[u] = (g + u) * TPW + sub;
+            const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(min(tok[u], ntok - 1)) * C);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) v[u][i] = __ldg(xr + l + LPT * i);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) s += (v[u][i].x + v[u][i].y) + (v[u][i].z + v[u][i].w);
+#pragma unroll
+            for (int o = LPT / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            const float mean = s * inv_c;
+            float ss = 0.f;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                v[u][i].x -= mean; v[u][i].y -= mean; v[u][i].z -= mean; v[u][i].w -= mean;
+                ss += (v[u][i].x * v[u][i].x + v[u][i].y * v[u][i].y) + (v[u][i].z * v[u][i].z + v[u][i].w * v[u][i].w);
+            }
+#pragma unroll
+            for (int o = LPT / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            const float rstd = rsqrtf(ss * inv_c + eps);
+            if (tok[u] >= ntok) continue;
+            uint2 pk[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                pk[i].x = pack_bf16x2(fmaf(v[u][i].x * rstd, gw[i].x, gb[i].x), fmaf(v[u][i].y * rstd, gw[i].y, gb[i].y));
+                pk[i].y = pack_bf16x2(fmaf(v[u][i].z * rstd, gw[i].z, gb[i].z), fmaf(v[u][i].w * rstd, gw[i].w, gb[i].w));
+            }
+            const int row = tok[u] / W;
+            const int w = tok[u] - row * W;
+            const int b = row / H;
+            const int h = row - b * H;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const int kh = kk >> 1, kw = kk & 1;
+                const int hh = h - kh, ww = w - kw;
+                if (hh < 0 || ww < 0) continue;
+                int ho = hh, wo = ww;
+                if (stride == 2) {
+                    if ((hh | ww) & 1) continue;
+                    ho = hh >> 1;
+                    wo = ww >> 1;
+                }
+                if (ho >= Ho || wo >= Wo) continue;
+                uint2* o = reinterpret_cast<uint2*>(out + ((static_cast<size_t>(b) * Ho + ho) * Wo + wo) * (4 * static_cast<size_t>(C)) +
+                                                    static_cast<size_t>(kk) * C);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[l + LPT * i] = pk[i];
+            }
+        }
+    }
+}
+
 }  // namespace cpn

@@ -198,7 +198,8 @@ def _mlp_operands(M, C, device, seed):
 
 
 @pytest.mark.parametrize("cg", ["1", "2"])
-@pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (128, 96), (129, 192), (46656, 384), (50176, 192)])
+@pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (128, 96), (129, 192), (46656, 384), (50176, 192),
+                                 (1, 96), (130, 384), (257, 192)])
 def test_mlp_fused(cuda_device, M, C, cg, monkeypatch):
     """One-kernel CNBlock MLP against (a) the two-GEMM path of this library (same arithmetic: bf16 hidden activations,
     fp32 accumulation) and (b) torch fp32. Several tiles per CTA at the large sizes; ragged last tiles."""
@@ -238,7 +239,8 @@ print(json.dumps(dict(vs_two_gemm=(x1 - x2).abs().max().item(), vs_torch=(x1 - r
     assert res["vs_torch"] <= max(2.0 * res["two_gemm_vs_torch"], 1e-2 * max(1.0, res["scale"])), res
 
 
-@pytest.mark.parametrize("stride,H,W,C", [(2, 16, 16, 96), (1, 14, 14, 192), (1, 9, 11, 384)])
+@pytest.mark.parametrize("stride,H,W,C", [(2, 16, 16, 96), (1, 14, 14, 192), (1, 9, 11, 384), (2, 7, 9, 96), (1, 3, 5, 192),
+                                            (1, 2, 2, 384), (2, 10, 10, 64), (1, 6, 7, 768)])
 def test_ln_im2col2(cuda_device, stride, H, W, C):
     g = torch.Generator().manual_seed(C)
     B = 2
