@@ -34,6 +34,7 @@ SIGNATURES = {
     "cpn_softmax_pool_arg": [_vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_pool_argmax_reduce": [_vp, _vp, _vp, _i, _vp, _i, _i, _vp],
     "cpn_topk_update": [_vp, _vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _vp, _vp],
+    "cpn_eval_batch": [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "cpn_head_tail": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_nhwc_to_nchw": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_nchw_to_nhwc": [_vp, _vp, _vp, _i, _i, _i, _vp],

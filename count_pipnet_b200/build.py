@@ -12,7 +12,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libcpnb200.so")
 SOURCES = ["api.cu"]
-HEADERS = ["ptx.cuh", "gemm_tcgen05.cuh", "gemm_tma_epi.cuh", "gelu_fast.cuh", "convnext_kernels.cuh", "dwconv_stats.cuh", "mlp_fused.cuh", "dwconv_tma.cuh", "head_kernels.cuh", "layout_kernels.cuh",
+HEADERS = ["ptx.cuh", "gemm_tcgen05.cuh", "gemm_tma_epi.cuh", "gelu_fast.cuh", "convnext_kernels.cuh", "dwconv_stats.cuh", "mlp_fused.cuh", "dwconv_tma.cuh", "head_kernels.cuh", "eval_kernels.cuh", "layout_kernels.cuh",
            os.path.join("..", "..", "include", "cpn_b200.h")]
 
 NVCC_FLAGS = [
@@ -39,12 +39,13 @@ def needs_build() -> bool:
 def build_library(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB_PATH
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + \
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH + ".tmp"] + \
         [os.path.join(CSRC, s) for s in SOURCES] + LINK_FLAGS
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
         raise RuntimeError("nvcc failed building libcpnb200.so: " + " ".join(cmd))
+    os.replace(LIB_PATH + ".tmp", LIB_PATH)  # a snapshot of the tree never sees a half-written library
     if verbose:
         sys.stderr.write(res.stderr)
     return LIB_PATH

@@ -19,6 +19,7 @@
 #include "dwconv_tma.cuh"
 #include "gemm_tcgen05.cuh"
 #include "gemm_tma_epi.cuh"
+#include "eval_kernels.cuh"
 #include "head_kernels.cuh"
 #include "layout_kernels.cuh"
 #include "mlp_fused.cuh"
@@ -137,6 +138,42 @@ int num_sms() {
     return n;
 }
 
+// Launch with programmatic dependent launch (and an optional CTA-pair cluster): the kernel may become resident and run
+// its on-chip prologue while the previous kernel of the stream drains. ONLY for kernels that execute ptx::pdl_wait()
+// before their first global access. Off unless CPN_PDL=1: measured on B200 (profiles/r01_pdl_ab.md) the 48-launch step
+// is 4.27 ms with it and 4.24 ms without -- the launch gaps it hides are smaller than what early-resident CTAs cost.
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("CPN_PDL"); return e != nullptr && atoi(e) != 0; }();
+    return on;
+}
+template <class... KArgs, class... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster,
+                       Args... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    unsigned n = 0;
+    if (cluster > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = cluster;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------------------------------------ GEMM dispatch
 struct GemmLaunch {
     CUtensorMap ta, tb, ta_lo, tb_lo;
@@ -235,24 +272,7 @@ int launch_gemm2_inst(const Gemm2Launch& g, cudaStream_t st) {
         CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         attr_done = true;
     }
-    if (CG == 1) {
-        kern<<<g.grid, S::THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.tout, g.p);
-    } else {
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof(cfg));
-        cfg.gridDim = dim3(g.grid);
-        cfg.blockDim = dim3(S::THREADS);
-        cfg.dynamicSmemBytes = S::TOTAL;
-        cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        CPN_CUDA(cudaLaunchKernelEx(&cfg, kern, g.ta, g.tb, g.tout, g.p));
-    }
+    CPN_CUDA(launch_pdl(kern, dim3(g.grid), dim3(S::THREADS), S::TOTAL, st, CG, g.ta, g.tb, g.tout, g.p));
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -459,11 +479,14 @@ int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat1
     // register cap = occupancy: 200 -> 10 warps per SM, 168 -> 12 (light spilling), 224 -> 8 (CPN_DWS_REGS, tuning)
     static const int regs = [] { const char* e = getenv("CPN_DWS_REGS"); return e == nullptr ? 200 : atoi(e); }();
     if (regs <= 168)
-        cpn::dwconv7_stats_kernel<C, 168><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 168>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
+                            stats, H, W, nstrips, rows));
     else if (regs <= 200)
-        cpn::dwconv7_stats_kernel<C, 200><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 200>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
+                            stats, H, W, nstrips, rows));
     else
-        cpn::dwconv7_stats_kernel<C, 224><<<grid, cpn::DWS_WARPS * 32, 0, st>>>(x, w49, bias, out, stats, H, W, nstrips, rows);
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 224>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
+                            stats, H, W, nstrips, rows));
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -485,24 +508,7 @@ int launch_mlp_inst(const MlpLaunch& g, cudaStream_t st) {
         CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         attr_done = true;
     }
-    if (CG == 1) {
-        kern<<<g.grid, S::THREADS, S::TOTAL, st>>>(g.tx, g.tw1, g.tw2, g.p);
-    } else {
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof(cfg));
-        cfg.gridDim = dim3(g.grid);
-        cfg.blockDim = dim3(S::THREADS);
-        cfg.dynamicSmemBytes = S::TOTAL;
-        cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        CPN_CUDA(cudaLaunchKernelEx(&cfg, kern, g.tx, g.tw1, g.tw2, g.p));
-    }
+    CPN_CUDA(launch_pdl(kern, dim3(g.grid), dim3(S::THREADS), S::TOTAL, st, CG, g.tx, g.tw1, g.tw2, g.p));
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -607,7 +613,8 @@ int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bia
             if (smem2 > 48 * 1024)
                 CPN_CUDA(cudaFuncSetAttribute(cpn::stem_ln_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               static_cast<int>(smem2)));
-            cpn::stem_ln_rows_kernel<<<grid2, cpn::STEM2_THREADS, smem2, st>>>(x, w, bias, ln_w, ln_b, out, B, H, W, Ho, Wo, eps);
+            CPN_CUDA(launch_pdl(cpn::stem_ln_rows_kernel, grid2, dim3(cpn::STEM2_THREADS), smem2, st, 1, x, w, bias, ln_w, ln_b,
+                                out, B, H, W, Ho, Wo, eps));
             CPN_CUDA(cudaGetLastError());
             return 0;
         });
@@ -826,9 +833,9 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
             long long want3 = (ntok + 16 * tpw - 1) / (16 * tpw);  // 8 warps x 2 passes x tpw tokens per CTA
             const int pgrid3 = static_cast<int>(want3 < cap ? want3 : cap);
             return submit(plan, stream, [=](cudaStream_t st) -> int {
-                if (C == 96) cpn::ln_im2col3_bf16_kernel<8><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
-                else if (C == 192) cpn::ln_im2col3_bf16_kernel<16><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
-                else cpn::ln_im2col3_bf16_kernel<32><<<pgrid3, 256, 0, st>>>(x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps);
+                if (C == 96) CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<8>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
+                else if (C == 192) CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<16>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
+                else CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<32>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
                 CPN_CUDA(cudaGetLastError());
                 return 0;
             });
@@ -969,9 +976,11 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
             if (smem > 48 * 1024)                                                                                      \
                 CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_reg_kernel<NVV, true>,                                 \
                                               cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));   \
-            cpn::softmax_pool_reg_kernel<NVV, true><<<grid, 256, smem, st>>>(z, mode, partial, partial_arg, HW, chunks); \
+            CPN_CUDA(launch_pdl(cpn::softmax_pool_reg_kernel<NVV, true>, grid, dim3(256), smem, st, 1, z, mode, partial,  \
+                                partial_arg, HW, chunks));                                                            \
         } else {                                                                                                       \
-            cpn::softmax_pool_reg_kernel<NVV, false><<<grid, 256, smem, st>>>(z, mode, partial, nullptr, HW, chunks);  \
+            CPN_CUDA(launch_pdl(cpn::softmax_pool_reg_kernel<NVV, false>, grid, dim3(256), smem, st, 1, z, mode, partial, \
+                                static_cast<int*>(nullptr), HW, chunks));                                              \
         }                                                                                                              \
         break;
             switch (nv) {
@@ -1027,6 +1036,31 @@ int cpn_topk_update(cpn_plan* plan, const float* pooled, const int* argmax, int 
     });
 }
 
+int cpn_eval_batch(cpn_plan* plan, const float* pooled, const float* out, const float* w, const long long* ys,
+                   float mult, float thr, int B, int P, int K, int* pred, float* pred_prob, float* max_score,
+                   int* any_size, int* pred_size, int* anz, int* top1, int* top5, unsigned long long* cm,
+                   unsigned char* relevant, int* protos_per_class, void* stream) {
+    if (pooled == nullptr || out == nullptr || w == nullptr || pred == nullptr || pred_prob == nullptr ||
+        max_score == nullptr || any_size == nullptr || pred_size == nullptr || anz == nullptr || top1 == nullptr ||
+        top5 == nullptr || relevant == nullptr || protos_per_class == nullptr)
+        return fail("cpn_eval_batch: missing operand");
+    if (B <= 0 || P <= 0 || K <= 0) return fail("cpn_eval_batch: bad shape B=%d P=%d K=%d", B, P, K);
+    cpn::EvalParams ep;
+    ep.pooled = pooled; ep.out = out; ep.w = w; ep.ys = ys; ep.mult = mult; ep.thr = thr;
+    ep.B = B; ep.P = P; ep.K = K; ep.pred = pred; ep.pred_prob = pred_prob; ep.max_score = max_score;
+    ep.any_size = any_size; ep.pred_size = pred_size; ep.anz = anz; ep.top1 = top1; ep.top5 = top5; ep.cm = cm;
+    ep.relevant = relevant;
+    set_info("eval_batch", 0.0, 4.0 * B * K * P + 4.0 * B * (P + K) + 2.0 * K * P);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        CPN_CUDA(cudaMemsetAsync(relevant, 0, static_cast<size_t>(K) * P, st));  // per-batch statistic
+        cpn::eval_batch_kernel<<<B, cpn::EVAL_THREADS, 0, st>>>(ep);
+        CPN_CUDA(cudaGetLastError());
+        cpn::eval_class_count_kernel<<<K, 128, 0, st>>>(relevant, protos_per_class, P);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
 int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, int inference, int use_ste,
                   int max_count, int encoding, const float* enc_w0, const float* enc_w1, const float* enc_w2,
                   const float* cls_w, const float* cls_b, float* pooled_out, float* logits_out, int B, int P, int D,
@@ -1062,7 +1096,7 @@ int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, in
         if (smem > 48 * 1024)
             CPN_CUDA(cudaFuncSetAttribute(cpn::head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(smem)));
-        cpn::head_tail_kernel<<<dim3(B, ks), 256, smem, st>>>(tp);
+        CPN_CUDA(launch_pdl(cpn::head_tail_kernel, dim3(B, ks), dim3(256), smem, st, 1, tp));
         CPN_CUDA(cudaGetLastError());
         return 0;
     });

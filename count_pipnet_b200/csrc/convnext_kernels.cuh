@@ -149,6 +149,8 @@ stem_ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, co
         gw[i] = __ldg(ln_w + i * 16 + cg);
         gb[i] = __ldg(ln_b + i * 16 + cg);
     }
+    ptx::pdl_wait();  // weights above are constants of the plan; the activations come from the previous kernel
+    ptx::pdl_launch_dependents();
     const int nrows = B * Ho;
     auto issue = [&](int r, int buf) {
         const int b = r / Ho, ho = r - b * Ho;
@@ -500,6 +502,8 @@ ln_im2col3_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
         gw[i] = __ldg(reinterpret_cast<const float4*>(ln_w) + l + LPT * i);
         gb[i] = __ldg(reinterpret_cast<const float4*>(ln_b) + l + LPT * i);
     }
+    ptx::pdl_wait();  // weights above are constants of the plan; the activations come from the previous kernel
+    ptx::pdl_launch_dependents();
     const float inv_c = 1.0f / static_cast<float>(C);
     for (int g = (blockIdx.x * (blockDim.x >> 5) + warp) * 2; g * TPW < ntok; g += 2 * nwarps) {
         float4 v[2][3];

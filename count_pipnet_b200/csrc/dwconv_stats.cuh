@@ -84,6 +84,8 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
 #pragma unroll
     for (int k = 0; k < 49; ++k) wr[k] = ldg_f2(w49 + k * C + c0);
     const float2 bs = ldg_f2(bias + c0);
+    ptx::pdl_wait();  // weights above are constants of the plan; the activations come from the previous kernel
+    ptx::pdl_launch_dependents();
 
     // column validity of the TW+6 inputs of a row (bit i: column w0-3+i inside the image)
     unsigned colmask = 0;

@@ -180,6 +180,8 @@ softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict
                         int* __restrict__ partial_arg, int HW, int chunks) {
     constexpr int P = NV * 128;
     extern __shared__ float s_pool[];  // [warps][P]
+    ptx::pdl_wait();
+    ptx::pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const int b = blockIdx.y;
@@ -306,6 +308,8 @@ struct TailParams {
 __global__ void __launch_bounds__(256)
 head_tail_kernel(const TailParams p) {
     extern __shared__ float s_buf[];
+    ptx::pdl_wait();
+    ptx::pdl_launch_dependents();
     float* s_pooled = s_buf;
     float* s_inter = s_buf + p.P;
     float* s_tmp = s_inter + p.D;

@@ -133,6 +133,9 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
+    // everything above is on-chip set-up; the operands come from the previous kernel of the stream
+    ptx::pdl_wait();
+    ptx::pdl_launch_dependents();
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer (one thread per CTA)

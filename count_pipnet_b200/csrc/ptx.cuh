@@ -201,6 +201,13 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
 __device__ __forceinline__ void cluster_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// Programmatic dependent launch. A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may become
+// resident while the previous kernel of the stream is still draining; pdl_wait() blocks until that kernel has
+// completed and its writes are visible (a no-op for a plain launch), so it goes after the on-chip prologue (barrier
+// initialisation, TMEM allocation, descriptor prefetch) and before the first global access. pdl_launch_dependents()
+// lets the NEXT kernel of the stream start its prologue once every CTA of this grid has executed it (or exited).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 // The pair's even CTA (the MMA leader) sees the same shared-memory offset with bit 24 of the address cleared.
 constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;
 // TMA load into THIS CTA's shared memory whose completion bytes are counted on the LEADER CTA's mbarrier.

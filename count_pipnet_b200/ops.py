@@ -188,6 +188,21 @@ def subsample2_bf16(x, out, B, H, W, Cc, plan=None):
     _lib.call("cpn_subsample2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())
 
 
+def eval_batch(pooled, out, weights, ys, mult, thr, res, cm=None, plan=None):
+    """Per-batch evaluation statistics: see cpn_eval_batch in include/cpn_b200.h. `res` is a dict of caller-allocated
+    outputs (pred, pred_prob, max_score, any_size, pred_size, anz, top1, top5 [B]; relevant [K, P] uint8;
+    protos_per_class [K]); cm [K, K] int64 accumulates."""
+    _need_cuda(pooled, out, weights, ys, cm, *res.values())
+    B, P = pooled.shape
+    K = out.shape[1]
+    if tuple(weights.shape) != (K, P):
+        raise _lib.CpnError(f"eval_batch: weights {tuple(weights.shape)} != (K, P) = ({K}, {P})")
+    _lib.call("cpn_eval_batch", _ph(plan), ptr(pooled), ptr(out), ptr(weights), ptr(ys), float(mult), float(thr), B, P,
+              K, ptr(res["pred"]), ptr(res["pred_prob"]), ptr(res["max_score"]), ptr(res["any_size"]),
+              ptr(res["pred_size"]), ptr(res["anz"]), ptr(res["top1"]), ptr(res["top5"]), ptr(cm),
+              ptr(res["relevant"]), ptr(res["protos_per_class"]), _stream())
+
+
 def topk_update(pooled, argmax, image_base, top_val, top_img, top_tok, top_cnt, plan=None):
     """Merges a batch into the running per-prototype top-k lists [k, P]: see cpn_topk_update in include/cpn_b200.h."""
     _need_cuda(pooled, argmax, top_val, top_img, top_tok, top_cnt)

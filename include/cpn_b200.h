@@ -144,6 +144,21 @@ int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* part
 int cpn_topk_update(cpn_plan* plan, const float* pooled, const int* argmax, int B, int P, int k, long long image_base,
                     float* top_val, long long* top_img, int* top_tok, int* top_cnt, void* stream);
 
+/* Per-batch evaluation statistics of the reference's test loop (replaces pipnet/test.py:82-137 and
+ * compute_local_explanation_sizes, pipnet/test.py:266-318, which build a [K,B,P] tensor and walk the batch on the host).
+ * pooled [B,P], out [B,K]: the forward's 2nd and 3rd outputs; w [K,P]: the weights the reference multiplies pooled with
+ * (_classification.weight as stored for PIP-Net; get_prototype_importance_per_class stacked for Count-PIP-Net);
+ * ys [B] int64 labels (NULL: no labels -- top1/top5 are 0 and cm is untouched); mult = normalization_multiplier;
+ * thr = 1e-3 in the reference. Per image: pred (first arg-max class), pred_prob (amax softmax(log1p(out**mult))),
+ * max_score (0 = abstained), any_size / pred_size (local explanation sizes), anz (|pooled| > thr), top1 / top5
+ * (label rank, ties towards the lower class). cm [K,K] uint64 ACCUMULATES cm[y][pred] += 1 (NULL to skip).
+ * relevant [K,P] bytes is scratch (zeroed by the call); protos_per_class [K] = prototypes with a non-zero thresholded
+ * contribution to the class in this batch (pipnet/test.py:108-113). Integer results are bit-exact. */
+int cpn_eval_batch(cpn_plan* plan, const float* pooled, const float* out, const float* w, const long long* ys,
+                   float mult, float thr, int B, int P, int K, int* pred, float* pred_prob, float* max_score,
+                   int* any_size, int* pred_size, int* anz, int* top1, int* top5, unsigned long long* cm,
+                   unsigned char* relevant, int* protos_per_class, void* stream);
+
 /* Chunk reduction, inference threshold (pipnet/pipnet.py:36) or round+clamp (pipnet/count_pipnet.py:90-97),
  * count encoding, and the non-negative classifier F.linear(x, relu(W), b) (pipnet/pipnet.py:70-71).
  * pooled_out [B,P] is the module's second return value; logits_out [B,K] the third. */
