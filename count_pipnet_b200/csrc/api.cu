@@ -1045,6 +1045,7 @@ int cpn_eval_batch(cpn_plan* plan, const float* pooled, const float* out, const 
         top5 == nullptr || relevant == nullptr || protos_per_class == nullptr)
         return fail("cpn_eval_batch: missing operand");
     if (B <= 0 || P <= 0 || K <= 0) return fail("cpn_eval_batch: bad shape B=%d P=%d K=%d", B, P, K);
+    if (P > 200 * 1024) return fail("cpn_eval_batch: P=%d too large", P);
     cpn::EvalParams ep;
     ep.pooled = pooled; ep.out = out; ep.w = w; ep.ys = ys; ep.mult = mult; ep.thr = thr;
     ep.B = B; ep.P = P; ep.K = K; ep.pred = pred; ep.pred_prob = pred_prob; ep.max_score = max_score;
@@ -1053,7 +1054,9 @@ int cpn_eval_batch(cpn_plan* plan, const float* pooled, const float* out, const 
     set_info("eval_batch", 0.0, 4.0 * B * K * P + 4.0 * B * (P + K) + 2.0 * K * P);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         CPN_CUDA(cudaMemsetAsync(relevant, 0, static_cast<size_t>(K) * P, st));  // per-batch statistic
-        cpn::eval_batch_kernel<<<B, cpn::EVAL_THREADS, 0, st>>>(ep);
+        if (P > 48 * 1024)
+            CPN_CUDA(cudaFuncSetAttribute(cpn::eval_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P));
+        cpn::eval_batch_kernel<<<B, cpn::EVAL_THREADS, static_cast<size_t>(P), st>>>(ep);
         CPN_CUDA(cudaGetLastError());
         cpn::eval_class_count_kernel<<<K, 128, 0, st>>>(relevant, protos_per_class, P);
         CPN_CUDA(cudaGetLastError());

@@ -35,7 +35,9 @@ struct EvalParams {
     unsigned char* relevant;  // [K, P] 1 where relu(pooled * w - thr) > 0 for some image of the batch (test.py:108-113)
 };
 
-constexpr int EVAL_THREADS = 256;
+constexpr int EVAL_THREADS = 1024;
+constexpr int EVAL_QLANES = 256;                          // prototype lanes ...
+constexpr int EVAL_KSLICES = EVAL_THREADS / EVAL_QLANES;  // ... times class slices
 
 __device__ __forceinline__ int block_sum_int(int v, int* s_slot) {
     v = __reduce_add_sync(0xffffffffu, v);
@@ -51,6 +53,7 @@ eval_batch_kernel(const EvalParams p) {
     __shared__ float s_f[2];
     __shared__ int s_pred;
     __shared__ int s_cnt[5];
+    extern __shared__ unsigned char s_any[];  // [P]: prototype relevant for any class of this image
     const int b = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const float* ob = p.out + static_cast<size_t>(b) * p.K;
     if (tid < 5) s_cnt[tid] = 0;
@@ -126,24 +129,51 @@ eval_batch_kernel(const EvalParams p) {
     }
     rank = block_sum_int(rank, &s_cnt[0]);
 
-    // ---- explanation sizes ----
+    // ---- explanation sizes: thread = (prototype lane, class slice); a warp covers 32 consecutive prototypes of one
+    // class slice, so the weight reads are coalesced 128-byte rows and a warp whose 32 pooled values are all zero
+    // (most of a PIP-Net's prototypes after the inference threshold) skips its classes altogether ----
     const float* pb = p.pooled + static_cast<size_t>(b) * p.P;
+    for (int q = tid; q < p.P; q += EVAL_THREADS) s_any[q] = 0;
+    __syncthreads();
+    const int kslice = tid / EVAL_QLANES, ql = tid % EVAL_QLANES;
+    const int kper = (p.K + EVAL_KSLICES - 1) / EVAL_KSLICES;
+    const int k0 = kslice * kper, k1 = min(p.K, k0 + kper);
     int n_anz = 0, n_any = 0, n_pred = 0;
-    for (int q = tid; q < p.P; q += EVAL_THREADS) {
-        const float pl = pb[q];
-        n_anz += fabsf(pl) > p.thr ? 1 : 0;
-        if (pl == 0.f) continue;  // 0 * w is 0 (or NaN for an infinite weight): never above the threshold
+    for (int q0 = ql - lane; q0 < p.P; q0 += EVAL_QLANES) {  // q0: warp-uniform
+        const int q = q0 + lane;
+        const bool valid = q < p.P;
+        const float pl = valid ? pb[q] : 0.f;
+        if (kslice == 0) n_anz += fabsf(pl) > p.thr ? 1 : 0;
+        if (!__any_sync(0xffffffffu, pl != 0.f)) continue;  // 0 * w is 0 (or NaN): never above the threshold
+        const float* wq = p.w + (valid ? q : 0);
         bool any = false;
-        for (int k = 0; k < p.K; ++k) {
-            const float s = __fmul_rn(pl, __ldg(p.w + static_cast<size_t>(k) * p.P + q));
+        int k = k0;
+        for (; k + 4 <= k1; k += 4) {
+            float wv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) wv[u] = __ldg(wq + static_cast<size_t>(k + u) * p.P);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float s = __fmul_rn(pl, wv[u]);
+                if (fabsf(s) > p.thr) {
+                    any = true;
+                    n_pred += (k + u == pred) ? 1 : 0;
+                }
+                if (valid && __fsub_rn(s, p.thr) > 0.f) p.relevant[static_cast<size_t>(k + u) * p.P + q] = 1;
+            }
+        }
+        for (; k < k1; ++k) {
+            const float s = __fmul_rn(pl, __ldg(wq + static_cast<size_t>(k) * p.P));
             if (fabsf(s) > p.thr) {
                 any = true;
                 n_pred += (k == pred) ? 1 : 0;
             }
-            if (__fsub_rn(s, p.thr) > 0.f) p.relevant[static_cast<size_t>(k) * p.P + q] = 1;  // same value from every image
+            if (valid && __fsub_rn(s, p.thr) > 0.f) p.relevant[static_cast<size_t>(k) * p.P + q] = 1;  // same value from every image
         }
-        n_any += any ? 1 : 0;
+        if (any && valid) s_any[q] = 1;  // several class slices may store the same 1
     }
+    __syncthreads();
+    for (int q = tid; q < p.P; q += EVAL_THREADS) n_any += s_any[q];
     n_anz = block_sum_int(n_anz, &s_cnt[1]);
     n_any = block_sum_int(n_any, &s_cnt[2]);
     n_pred = block_sum_int(n_pred, &s_cnt[3]);
