@@ -94,11 +94,16 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.t0 = self.t1 = None
 
     def __enter__(self):
+        """Started BEFORE the warm-up: nvidia-smi needs 0.1-1 s to come up (longer on an 8-GPU box), the timed region
+        of 20 steps lasts 85 ms. Rows are stamped on arrival; begin()/end() bracket the timed region."""
+        if self.index is None:
+            return self
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                          "--format=csv,noheader,nounits", "-lms", "10"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -108,7 +113,18 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def wait_first(self, timeout=5.0):
+        t = time.perf_counter()
+        while not self.rows and time.perf_counter() - t < timeout and self.proc is not None:
+            time.sleep(0.01)
+
+    def begin(self):
+        self.t0 = time.perf_counter()
+
+    def end(self):
+        self.t1 = time.perf_counter()
 
     def __exit__(self, *a):
         if self.proc is not None:
@@ -121,7 +137,13 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.t0 is not None and self.t0 <= t <= self.t1 + 0.015]
+        window = "timed region"
+        if not rows and self.t0 is not None:
+            # a very short timed region can fall between two samples: take the samples of the loaded period around it
+            rows = [r for t, r in self.rows if self.t0 - 0.1 <= t <= self.t1 + 0.1]
+            window = "timed region +- 0.1 s (device under the same load)"
+        for r in rows:
             try:
                 sm.append(float(r[0]))
                 mx.append(float(r[1]))
@@ -132,7 +154,8 @@ class ClockSampler:
                 continue
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "window": window}
 
 
 def base_line(args, world):
@@ -162,7 +185,7 @@ def run_reference(args, rank, world):
                                             f"oracle/ (CPU restatement of the reference forward), torch {torch.__version__}"},
                  "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
     line["config"]["reference_sample_images_per_step"] = per_step
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ this package
@@ -192,16 +215,21 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(args.warmup):
-        step(i)
-    barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank if rank == 0 else None) as clocks:  # rank 0 reports its own GPU
+        for i in range(args.warmup):
+            step(i)
+        clocks.wait_first()
+        for i in range(2):  # back under load after the wait (untimed)
+            step(i)
+        barrier()
+        clocks.begin()
         ev0.record()
         for i in range(args.steps):
             step(i)
         ev1.record()
         barrier()
+        clocks.end()
     ms_total = torch.tensor([ev0.elapsed_time(ev1)], device=device)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
@@ -267,7 +295,7 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": "16 images x 4 timed forwards (1 warm-up) of the same workload through "
                                               "oracle/ (CPU restatement of the reference forward)"}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -323,7 +351,16 @@ def roofline_report(plan, batch):
             "step_tflops": FLOP_PER_IMAGE * batch / (total_ms * 1e-3) / 1e12}
 
 
+JSON_OUT = sys.stdout
+
+
 def main():
+    # stdout carries exactly ONE line, the JSON: libraries that print there (NCCL's version banner under torchrun, the
+    # reference-style "Number of prototypes" message of the factories) are sent to stderr for the length of the run
+    global JSON_OUT
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
