@@ -140,3 +140,27 @@ def test_eval_batch_full_size_properties(cuda_device):
     st = reference_eval.batch_statistics(pooled, out, W, ys, 2.0)
     assert torch.equal(first["any_size"].cpu().long(), st["any_size"].long())
     assert torch.equal(first["protos_per_class"].cpu().long(), st["protos_per_class"].long())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,P,K", [(3, 37, 7), (1, 5, 1), (5, 1030, 3), (2, 33, 1500)])
+def test_eval_batch_odd_shapes(cuda_device, B, P, K):
+    """Ragged sizes: P not a multiple of the 32-lane prototype groups, fewer classes than class slices, more classes
+    than threads, a single image; labels out of range are skipped (no confusion-matrix entry, no top-k hit)."""
+    g = torch.Generator().manual_seed(100 + B + P + K)
+    W = torch.where(torch.rand(K, P, generator=g) < 0.3, torch.randn(K, P, generator=g) * 2, torch.zeros(()))
+    pooled = torch.where(torch.rand(B, P, generator=g) < 0.5, torch.zeros(()), torch.rand(B, P, generator=g))
+    out = pooled @ torch.relu(W).t()
+    ys = torch.randint(0, K, (B,), generator=g)
+    ev = eval_metrics.BatchEvaluator(K, P, cuda_device)
+    res = ev.update(pooled.to(cuda_device), out.to(cuda_device), W.to(cuda_device), ys.to(cuda_device), 2.0)
+    st = reference_eval.batch_statistics(pooled, out, W, ys, 2.0)
+    for k in ("pred", "any_size", "pred_size", "anz", "top1", "top5", "protos_per_class"):
+        assert torch.equal(res[k].cpu().long(), st[k].long()), k
+    torch.testing.assert_close(res["pred_prob"].cpu(), st["pred_prob"], rtol=1e-5, atol=1e-7)
+    assert np.array_equal(ev.cm.cpu().numpy(), st["cm"])
+    bad = torch.full((B,), K, dtype=torch.int64)  # out-of-range labels
+    ev2 = eval_metrics.BatchEvaluator(K, P, cuda_device)
+    res2 = ev2.update(pooled.to(cuda_device), out.to(cuda_device), W.to(cuda_device), bad.to(cuda_device), 2.0)
+    assert int(ev2.cm.sum()) == 0 and int(res2["top1"].sum()) == 0 and int(res2["top5"].sum()) == 0
+    assert torch.equal(res2["pred"].cpu().long(), st["pred"].long())
