@@ -117,3 +117,49 @@ def test_synth_weights_are_deterministic():
     assert all(torch.equal(a[k], b[k]) for k in a)
     w = a["_classification.weight"]
     assert ((w > 0).sum(1) == 8).all() and float(a["_multiplier"]) == 2.0
+
+
+# ---------------------------------------------------------------------------------------------- checkpoint compatibility
+def _state_key_table():
+    import json
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "state_dict_keys.json")))
+
+
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_state_dict_matches_reference_models(name):
+    """Ordered keys, shapes and dtypes equal those of the REAL reference model of the same configuration
+    (tests/golden/state_dict_keys.json, written by make_golden_state_keys.py from /root/reference): a reference
+    checkpoint loads with strict=True (util/checkpoint_manager.py:66)."""
+    ref = _state_key_table()[name]
+    mine = [[k, list(v.shape), str(v.dtype)] for k, v in cases.build(cases.CASES[name], my_pipnet, my_count).state_dict().items()]
+    assert [r[0] for r in mine] == [r[0] for r in ref]
+    assert mine == ref
+
+
+def test_load_reference_checkpoint_prefixes(tmp_path):
+    from count_pipnet_b200 import checkpoint as ck
+    case = cases.CASES["count_linear_softmax"]
+    src = cases.build(case, my_pipnet, my_count)
+    with torch.no_grad():
+        for p in src.parameters():
+            p.add_(0.25)
+    wrapped_state = {"module." + k: v.clone() for k, v in src.state_dict().items()}  # as nn.DataParallel saves it
+    path = tmp_path / "net_trained"
+    torch.save({"model_state_dict": wrapped_state, "epoch": 3, "accuracy": 0.5}, path)
+    # bare model <- DataParallel checkpoint file
+    dst = cases.build(case, my_pipnet, my_count)
+    res = ck.load_reference_checkpoint(dst, str(path))
+    assert not res.missing_keys and not res.unexpected_keys
+    for (k, a), (_, b) in zip(src.state_dict().items(), dst.state_dict().items()):
+        assert torch.equal(a, b), k
+    # wrapped model <- bare state dict
+    dst2 = torch.nn.DataParallel(cases.build(case, my_pipnet, my_count))
+    ck.load_reference_checkpoint(dst2, src.state_dict())
+    assert torch.equal(dst2.module._classification.weight, src._classification.weight)
+    # mismatches raise as in the reference (strict=True)
+    broken = dict(wrapped_state)
+    broken.pop("module._classification.weight")
+    with pytest.raises(RuntimeError):
+        ck.load_reference_checkpoint(cases.build(case, my_pipnet, my_count), {"model_state_dict": broken})
+    with pytest.raises(ValueError):
+        ck.load_reference_checkpoint(dst, {"epoch": 1})

@@ -177,3 +177,35 @@ def test_weight_mutation_is_seen(cuda_device):
         model._net.features[1][0].block[3].weight.mul_(1.5)
         _, _, out3 = model(x, inference=True)
         assert not torch.equal(out3, out2)
+
+
+def test_reference_checkpoint_load_is_seen(cuda_device, tmp_path):
+    """A DataParallel-style reference checkpoint (util/checkpoint_manager.py:170-180) loaded after a first forward:
+    load_state_dict copies in place, the packed kernel weights must follow, and the result equals the oracle run on
+    the checkpoint's weights."""
+    from count_pipnet_b200 import checkpoint as ck
+    case = cases.CASES["count_linear_softmax"]
+    src = cases.build(case, my_pipnet, my_count)
+    g = torch.Generator().manual_seed(3)
+    with torch.no_grad():
+        for p in src._net.parameters():
+            p.mul_(1.0 + 0.05 * torch.rand(p.shape, generator=g))
+        src._classification.weight.mul_(1.5)
+    path = tmp_path / "net_trained_last"
+    torch.save({"model_state_dict": {"module." + k: v for k, v in src.state_dict().items()}, "epoch": 1}, path)
+    model = cases.build(case, my_pipnet, my_count).to(cuda_device)
+    model.cpn_precision = "fp32"
+    x = cases.inputs(case)
+    with torch.no_grad():
+        _, _, out_before = model(x.to(cuda_device), inference=True)
+        ck.load_reference_checkpoint(model, str(path))
+        _, pooled, out = model(x.to(cuda_device), inference=True)
+    sd = {k: v.detach().cpu() for k, v in src.state_dict().items()}
+    ref = oracle.forward(sd, cases.oracle_cfg(case), x, inference=True)
+    assert not torch.equal(out, out_before)
+    mism = int((pooled.cpu() != ref[1]).sum())
+    # counts are exact in the parity cases (tests above); here the weights are freshly perturbed, so one spatial sum may
+    # sit within 1e-4 of a rounding boundary -- what this test pins is that the NEW weights are the ones used
+    assert mism <= 1
+    if mism == 0:
+        assert rel(out.cpu().numpy(), ref[2].numpy()) <= 1e-4
