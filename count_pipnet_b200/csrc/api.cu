@@ -14,6 +14,9 @@
 #include <string>
 #include <vector>
 
+#ifndef CPN_DWS_TW_DEFAULT
+#define CPN_DWS_TW_DEFAULT 4
+#endif
 #include "convnext_kernels.cuh"
 #include "dwconv_stats.cuh"
 #include "dwconv_tma.cuh"
@@ -473,12 +476,23 @@ int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, d
 }  // namespace
 
 namespace {
+// Strip width (output columns per lane). A warp's registers live in ONE of the SM's four 16K-register partitions, so
+// the resident warps per scheduler are floor(512 / registers per thread): 2 at 169-255 registers (TW = 4: 98 weight +
+// 56 accumulator + 20 input registers), 3 at <= 168 (TW = 3: 42 accumulators). CPN_DWS_TW selects (tools/run_op.py).
+int dws_tw() {
+    static const int tw = [] { const char* e = getenv("CPN_DWS_TW"); return e == nullptr ? CPN_DWS_TW_DEFAULT : atoi(e); }();
+    return tw == 3 ? 3 : 4;
+}
+
 template <int C>
 int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
                int nstrips, int rows, dim3 grid, cudaStream_t st) {
-    // register cap = occupancy: 200 -> 10 warps per SM, 168 -> 12 (light spilling), 224 -> 8 (CPN_DWS_REGS, tuning)
+    // register cap = occupancy (see above): 200 -> 2 warps per scheduler, 168 -> 3 (spills at TW = 4; CPN_DWS_REGS, tuning)
     static const int regs = [] { const char* e = getenv("CPN_DWS_REGS"); return e == nullptr ? 200 : atoi(e); }();
-    if (regs <= 168)
+    if (dws_tw() == 3)
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 168, 3>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
+                            stats, H, W, nstrips, rows));
+    else if (regs <= 168)
         CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 168>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
                             stats, H, W, nstrips, rows));
     else if (regs <= 200)
@@ -681,13 +695,14 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
     if (C != 96 && C != 192 && C != 384 && C != 768)
         return fail("cpn_dwconv7_stats: C=%d is not a ConvNeXt-tiny width (96, 192, 384, 768)", C);
     if (B <= 0 || B > 65535 || H <= 0 || W <= 0) return fail("cpn_dwconv7_stats: bad shape B=%d H=%d W=%d", B, H, W);
-    const int nstrips = (W + 3) / 4;
+    const int tw = dws_tw();
+    const int nstrips = (W + tw - 1) / tw;
     const int warps = (nstrips * (C / 32) + 1) / 2;  // a warp = two (strip, 32-channel group) units
     const int gx = (warps + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
     // row segments: every segment pays 6 halo rows of loads AND of FMAs (the body is branch-free), so split H only
     // when the grid would not give each SM its two resident CTAs a few times over
     int nseg = 1;
-    while (static_cast<long long>(gx) * nseg * B < 5LL * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
+    while (static_cast<long long>(gx) * nseg * B < (tw == 3 ? 6LL : 5LL) * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
     if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knobs (tools/run_op.py)
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;

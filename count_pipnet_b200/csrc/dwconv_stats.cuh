@@ -31,7 +31,10 @@
 namespace cpn {
 
 constexpr int DWS_WARPS = 2;   // warps per CTA (independent of each other)
-constexpr int DWS_CTAS_PER_SM = 5;  // 10 warps per SM at <= 204 registers: B=64 then needs 2 / 2 / 2 / 4 waves per stage
+// Residency (ncu, profiles/r01_ncu_full_v10.md): a warp's registers sit in ONE of the SM's four 16K-register partitions, so at
+// 192 registers per thread 2 warps fit per scheduler = 8 warps = 4 CTAs per SM (not the 5 that 65536 / (64 * 192) suggests);
+// B=64 then runs 2.4 / 2.4 / 2.3 / 4.5 waves per stage. 3 warps per scheduler need <= 168 registers (TW = 3 variant below).
+constexpr int DWS_CTAS_PER_SM = 4;
 constexpr int DWS_TW = 4;      // output columns per lane
 constexpr int DWS_DEPTH = 3;   // rows in flight ahead of the one being consumed
 constexpr int DWS_NSLOT = DWS_DEPTH + 1;
@@ -53,13 +56,13 @@ struct StaticFor<N, N> {
 
 __device__ __forceinline__ float2 ldg_f2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
-template <int C, int MAXREG>
+template <int C, int MAXREG, int TW = DWS_TW>
 __global__ void __launch_bounds__(DWS_WARPS * 32) __maxnreg__(MAXREG)
 dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49, const float* __restrict__ bias,
                      __nv_bfloat16* __restrict__ out, float* __restrict__ stats, int H, int W, int nstrips,
                      int rows_per_seg) {
     static_assert(C % 32 == 0, "32-channel groups");
-    constexpr int TW = DWS_TW;
+    static_assert(TW >= 1 && TW <= 4, "the statistics butterfly carries 2 * TW <= 8 values");
     constexpr int NPART = C / 32;
     constexpr int NIN = TW + 6;
     constexpr int NT = DWS_WARPS * 32;
@@ -148,7 +151,7 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
     __nv_bfloat16* out_p = out + pix00 * C + c0;
     const int sidx = hl >> 1;  // statistics value this lane ends up holding: 2 * t + which
     float* st_p = stats + ((pix00 + (sidx >> 1)) * NPART + cg) * 2 + (sidx & 1);
-    const bool st_ok = live && (lane & 1) == 0 && w0 + (sidx >> 1) < W;
+    const bool st_ok = live && (lane & 1) == 0 && (sidx >> 1) < TW && w0 + (sidx >> 1) < W;
     unsigned store_mask = 0;
 #pragma unroll
     for (int t = 0; t < TW; ++t)
@@ -196,7 +199,9 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
             if (r >= 6) {
                 // output row r - 6 is complete (slot (j + 1) % 7)
                 const int s = (j + 1) % 7;
-                float a[2 * TW];
+                float a[8];  // 2 * TW values, zero-padded to the butterfly's 8
+#pragma unroll
+                for (int i = 2 * TW; i < 8; ++i) a[i] = 0.f;
 #pragma unroll
                 for (int t = 0; t < TW; ++t) {
                     const uint32_t pk = pack_bf16x2(acc[s][t].x, acc[s][t].y);
