@@ -1,6 +1,8 @@
 #!/usr/bin/env python
-"""Benchmark of the forward hot path: images/sec of `net(x, inference=True)` for PIP-Net ConvNeXt-tiny (26x26 grid),
-224^2, 768 prototypes, 200 classes, batch 64 per GPU (BASELINE.json configs[1]); weak scaling over N GPUs.
+"""Benchmark of the forward hot path: images/sec of `net(x, inference=True)`. Default workload: PIP-Net ConvNeXt-tiny
+(26x26 grid), 224^2, 768 prototypes, 200 classes, batch 64 per GPU (BASELINE.json configs[1]); weak scaling over N GPUs.
+`--config cfg1|cfg3|cfg4|cfg5` times the other BASELINE.json workloads at their stated per-GPU batch, `--precision fp32`
+the exact-parity mode (the default line carries it as the `fp32_mode` block).
 
     python bench.py --gpus 1 --steps 20 --warmup 5                      # this package (sm_100a kernels)
     python bench.py --impl reference --gpus 1 --steps 20 --warmup 5     # reference arithmetic on the host cores
@@ -27,9 +29,6 @@ sys.path.insert(0, ROOT)
 
 METRIC = "images/sec fwd (ConvNeXt-tiny PIP-Net, 224^2)"
 UNIT = "images/s"
-WORKLOAD = "PIP-Net ConvNeXt-tiny-26 224x224, 768 prototypes, 200 classes, batch 64 per GPU (BASELINE.json configs[1])"
-FLOP_PER_IMAGE = 40.094e9  # 2*MAC of conv/linear layers (torch FlopCounterMode on the reference)
-CLASSES, SIZE = 200, 224
 
 
 def quiet():
@@ -48,43 +47,108 @@ def load_peaks():
     return dict(hbm_gbs=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
 
 
-def build_model(device, precision):
-    from count_pipnet_b200 import synth
-    from count_pipnet_b200.pipnet import pipnet as my_pipnet
-    with quiet():
-        model, _ = my_pipnet.get_pipnet(CLASSES, synth.make_args(net="convnext_tiny_26", num_features=0))
-    synth.load_synth(model, seed=0)
-    model = model.eval().to(device)
+def cfg_of(args):
+    from count_pipnet_b200 import configs
+    return configs.CONFIGS[args.config]
+
+
+def metric_name(args):
+    """BASELINE.json's metric is quoted on cfg2; the other configs report the same quantity for their own model."""
+    return METRIC if args.config == "cfg2" else f"images/sec fwd ({args.config})"
+
+
+def build_model(args, device, precision):
+    from count_pipnet_b200 import configs
+    model = configs.build_model(args.config).to(device)
     model.cpn_precision = precision
-    model.materialize_proto_map = False  # north star: the map is written only when the caller asks for it
+    # north star: the map is written only when the caller asks for it (cfg5 asks)
+    model.materialize_proto_map = bool(cfg_of(args)["materialize_map"])
     return model
 
 
-def oracle_state_dict():
-    """Seeded weights for the CPU arms, generated from key/shape only (no product module runs on that path)."""
-    from count_pipnet_b200 import synth
-    from count_pipnet_b200.pipnet import pipnet as my_pipnet
-    with quiet():
-        model, _ = my_pipnet.get_pipnet(CLASSES, synth.make_args(net="convnext_tiny_26", num_features=0))
-    synth.load_synth(model, seed=0)
+def oracle_state_dict(args):
+    """Seeded weights for the CPU / eager arms, generated from key/shape only (no product kernel runs on that path)."""
+    from count_pipnet_b200 import configs
+    model = configs.build_model(args.config)
     return {k: v.detach() for k, v in model.state_dict().items()}
 
 
-ORACLE_CFG = dict(model="pipnet", net="convnext_tiny_26")
+def oracle_noise(args, cfg, n, device="cpu"):
+    if cfg["args"].get("activation") != "gumbel_softmax":
+        return None
+    grid = cfg["size"] // 8  # three feature modules: stem /4, one stride-2 downsample
+    g = torch.Generator(device="cpu").manual_seed(7)
+    return (-torch.empty(n, cfg["prototypes"], grid, grid).exponential_(generator=g).log()).to(device)
 
 
-def time_oracle(sd, images_per_step, steps, warmup):
-    """Reference arithmetic (oracle port of pipnet/pipnet.py:31-41 + torchvision ConvNeXt) on the host cores."""
+def time_oracle(args, sd, images_per_step, steps, warmup):
+    """Reference arithmetic (oracle port of pipnet/pipnet.py:31-41, pipnet/count_pipnet.py:70-110 + torchvision ConvNeXt /
+    features/resnet_features.py) on the host cores."""
     import oracle
-    from count_pipnet_b200 import synth
-    x = synth.synth_images(images_per_step, SIZE, seed=1234)
+    from count_pipnet_b200 import configs, synth
+    cfg = cfg_of(args)
+    x = synth.synth_images(images_per_step, cfg["size"], seed=1234)
+    noise = oracle_noise(args, cfg, images_per_step)
+    ocfg = configs.oracle_cfg(args.config)
     for _ in range(warmup):
-        oracle.forward(sd, ORACLE_CFG, x, inference=True)
+        oracle.forward(sd, ocfg, x, inference=True, gumbel_noise=noise)
     t0 = time.perf_counter()
     for _ in range(steps):
-        oracle.forward(sd, ORACLE_CFG, x, inference=True)
+        oracle.forward(sd, ocfg, x, inference=True, gumbel_noise=noise)
     dt = time.perf_counter() - t0
     return images_per_step * steps / dt, dt / steps * 1e3
+
+
+def time_gpu_eager(args, device, batch, steps=5, warmup=2):
+    """The "beat this" number: the reference arithmetic as stock PyTorch eager on
+    the same B200 -- the oracle's torch.nn.functional backbone with all tensors on the GPU (fp32 NCHW, cuDNN / cuBLAS
+    under torch's default TF32 settings, which are reported), and the reference head in torch ops. CUDA-event timed."""
+    import oracle
+    import oracle.reference_heads as rh
+    import torch.nn.functional as F
+    from count_pipnet_b200 import configs, synth
+    cfg = cfg_of(args)
+    ocfg = configs.oracle_cfg(args.config)
+    sd = {k: v.to(device) for k, v in oracle_state_dict(args).items()}
+    xs = [synth.synth_images(batch, cfg["size"], seed=3000 + i).to(device) for i in range(4)]
+    act = ocfg["activation"] if cfg["model"] == "count_pipnet" else "softmax"
+
+    def fwd(x):
+        with torch.no_grad():
+            feats = oracle.backbone(sd, ocfg, x)
+            noise = None
+            if act == "gumbel_softmax":  # F.gumbel_softmax's draw (count_pipnet_utils.py:36-38)
+                shape = (x.shape[0], cfg["prototypes"], feats.shape[2], feats.shape[3])
+                noise = -torch.empty(shape, device=device).exponential_().log()
+            proto = rh.add_on(sd, feats, act, noise, 1.0, hard=True)
+            if cfg["model"] == "pipnet":
+                return rh.pipnet_head(sd, proto, True)
+            m = cfg["max_count"]
+            clamped = proto.sum(dim=(2, 3)).round().clamp(0, m)  # pipnet/count_pipnet.py:88-104
+            kind = ocfg["intermediate_layer"]
+            if kind == "onehot":  # count_pipnet_utils.py:141-185 in torch ops
+                idx = (clamped.long() - 1).clamp(0, m - 1)
+                enc = (F.one_hot(idx, m).float() * (clamped > 0.1)[..., None]).flatten(1)
+            else:
+                enc = rh.intermediate(sd, kind, clamped, m, cfg["use_ste"])
+            return clamped, rh.non_neg_linear(sd, enc)
+
+    for i in range(warmup):
+        fwd(xs[i % 4])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fwd(xs[i % 4])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": batch / (ms / 1e3), "unit": UNIT, "ms_per_step": ms, "batch": batch, "steps": steps,
+            "what": "reference arithmetic in stock PyTorch eager on this GPU (oracle's torch.nn.functional forward, fp32 "
+                    "NCHW, cuDNN/cuBLAS), inputs resident, CUDA events",
+            "allow_tf32": {"cudnn": bool(torch.backends.cudnn.allow_tf32),
+                           "matmul": bool(torch.backends.cuda.matmul.allow_tf32)},
+            "torch": torch.__version__}
 
 
 class ClockSampler:
@@ -158,12 +222,16 @@ class ClockSampler:
                 "window": window}
 
 
-def base_line(args, world):
-    return {"metric": METRIC, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "global_batch": args.batch * world,
-                       "image_size": SIZE, "prototypes": 768, "classes": CLASSES,
-                       "weights": "seeded synthetic (count_pipnet_b200/synth.py), random init shape of ConvNeXt-tiny"}}
+def base_line(args, world, batch):
+    cfg = cfg_of(args)
+    strong = "global_batch" in cfg and world > 1
+    return {"metric": metric_name(args), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "data": "synthetic",
+            "config": {"workload": cfg["label"], "name": args.config, "batch_per_gpu": batch,
+                       "global_batch": batch * world, "image_size": cfg["size"], "prototypes": cfg["prototypes"],
+                       "classes": cfg["classes"],
+                       "weights": "seeded synthetic (count_pipnet_b200/synth.py), random-init shapes of the named model"},
+            "env_knobs": {k: v for k, v in sorted(os.environ.items()) if k.startswith("CPN_")}}
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
@@ -173,12 +241,14 @@ def run_reference(args, rank, world):
     tests/golden) on the host cores with all threads. Rank 0 only."""
     if rank != 0:
         return
+    from count_pipnet_b200 import configs
+    batch = args.batch or configs.batch_per_gpu(args.config, world)
     torch.set_num_threads(os.cpu_count() or 1)
-    sd = oracle_state_dict()
-    rate, _ = time_oracle(sd, 2, 1, 1)  # probe, then size a bounded per-step sample: whole run about two minutes
-    per_step = max(1, min(args.batch, int(rate * 120.0 / max(args.steps + args.warmup, 1))))
-    value, ms = time_oracle(sd, per_step, args.steps, args.warmup)
-    line = base_line(args, world)
+    sd = oracle_state_dict(args)
+    rate, _ = time_oracle(args, sd, 2, 1, 1)  # probe, then size a bounded per-step sample: whole run about two minutes
+    per_step = max(1, min(batch, int(rate * 120.0 / max(args.steps + args.warmup, 1))))
+    value, ms = time_oracle(args, sd, per_step, args.steps, args.warmup)
+    line = base_line(args, world, batch)
     line.update({"impl": "reference", "value": value, "ms_per_step": ms, "dtype": "f32",
                  "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                                   "sample": f"{per_step} images per step x {args.steps} steps of the same workload, "
@@ -189,58 +259,70 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------ this package
+def timed_steps(step, steps, warmup, barrier, world, device, clocks=None):
+    """W untimed + K timed steps between barrier + synchronize, CUDA events, MAX over ranks. Returns ms per step."""
+    import torch.distributed as dist
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for i in range(warmup):
+        step(i)
+    if clocks is not None:
+        clocks.wait_first()
+        for i in range(2):  # back under load after the wait (untimed)
+            step(i)
+    barrier()
+    if clocks is not None:
+        clocks.begin()
+    ev0.record()
+    for i in range(steps):
+        step(i)
+    ev1.record()
+    barrier()
+    if clocks is not None:
+        clocks.end()
+    ms_total = torch.tensor([ev0.elapsed_time(ev1)], device=device)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    return float(ms_total.item()) / steps
+
+
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
-    from count_pipnet_b200 import engine
+    from count_pipnet_b200 import configs, engine, sharding, synth
+    cfg = cfg_of(args)
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
-    model = build_model(device, args.precision)
-    from count_pipnet_b200 import synth
-    B = args.batch
-    nrot = 8  # 8 resident batches = 308 MB at B=64 > 126 MB L2: inputs never come from cache
-    xs = [synth.synth_images(B, SIZE, seed=1000 + rank * 100 + i).to(device) for i in range(nrot)]
-    from count_pipnet_b200 import sharding
+    B = args.batch or configs.batch_per_gpu(args.config, world)
+    size, classes, protos = cfg["size"], cfg["classes"], cfg["prototypes"]
+    in_bytes = B * 3 * size * size * 4
+    nrot = max(2, min(8, -(-(160 << 20) // in_bytes)))  # rotating resident batches: together larger than the 126 MB L2
+    xs = [synth.synth_images(B, size, seed=1000 + rank * 100 + i).to(device) for i in range(nrot)]
 
-    def step(i):
-        with torch.no_grad():
-            _, pooled, out = model(xs[i % nrot], inference=True)
-        if world > 1:  # the only exchange of the path: gather logits and pooled scores
-            pooled, out = sharding.gather_outputs(pooled, out, B * world)
-        return pooled, out
+    def make_step(model):
+        def step(i):
+            with torch.no_grad():
+                _, pooled, out = model(xs[i % nrot], inference=True)
+            if world > 1:  # the only exchange of the path: gather logits and pooled scores (SURVEY 8(e))
+                pooled, out = sharding.gather_outputs(pooled, out, B * world)
+            return pooled, out
+        return step
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    model = build_model(args, device, args.precision)
     with ClockSampler(local_rank if rank == 0 else None) as clocks:  # rank 0 reports its own GPU
-        for i in range(args.warmup):
-            step(i)
-        clocks.wait_first()
-        for i in range(2):  # back under load after the wait (untimed)
-            step(i)
-        barrier()
-        clocks.begin()
-        ev0.record()
-        for i in range(args.steps):
-            step(i)
-        ev1.record()
-        barrier()
-        clocks.end()
-    ms_total = torch.tensor([ev0.elapsed_time(ev1)], device=device)
-    if world > 1:
-        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
-    ms_step = float(ms_total.item()) / args.steps
+        ms_step = timed_steps(make_step(model), args.steps, args.warmup, barrier, world, device, clocks)
     value = world * B / (ms_step / 1e3)
 
     # ---- end to end: pinned host batches -> H2D -> forward -> D2H of logits + pooled, copy overlapped on a side stream
-    host = [synth.synth_images(B, SIZE, seed=2000 + i).pin_memory() for i in range(4)]
-    dev_in = [torch.empty(B, 3, SIZE, SIZE, device=device) for _ in range(2)]
-    host_logits = torch.empty(B, CLASSES).pin_memory()
-    host_pooled = torch.empty(B, 768).pin_memory()
+    host = [synth.synth_images(B, size, seed=2000 + i).pin_memory() for i in range(4)]
+    dev_in = [torch.empty(B, 3, size, size, device=device) for _ in range(2)]
+    host_logits = torch.empty(B, classes).pin_memory()
+    host_pooled = torch.empty(B, protos).pin_memory()
     copy_stream = torch.cuda.Stream(device)
     main_stream = torch.cuda.current_stream(device)
 
@@ -272,28 +354,45 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = world * B * args.steps / float(e2e_s.item())
 
-    line = base_line(args, world)
+    line = base_line(args, world, B)
     line.update({"value": value, "ms_per_step": ms_step, "dtype": "bf16" if args.precision == "bf16" else "bf16x3",
                  "clocks": clocks.summary(),
-                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * 3 * SIZE * SIZE * 4,
-                         "d2h_bytes_per_step": B * (CLASSES + 768) * 4}})
+                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
+                         "d2h_bytes_per_step": B * (classes + protos) * 4}})
     line["config"].update({"precision_mode": args.precision, "parallelism": f"dp{world} (batch sharded, no data-path "
-                           "collective except the logits/pooled all-gather)",
-                           "l2_policy": f"inputs rotate over {nrot} resident batches ({nrot * B * 3 * SIZE * SIZE * 4 >> 20} MiB > L2); "
-                                        "activations per step exceed L2",
-                           "proto_map": "not materialised (caller did not ask for it)"})
+                           "collective except one packed logits+pooled all-gather)",
+                           "l2_policy": f"inputs rotate over {nrot} resident batches ({nrot * in_bytes >> 20} MiB > L2)",
+                           "proto_map": "materialised [B,P,H,W] fp32 every step (the caller asks for it)"
+                                        if cfg["materialize_map"] else "not materialised (caller did not ask for it)",
+                           "cuda_graph": bool(engine.USE_GRAPHS)})
 
+    st = engine.state_for(model, device)
+    rec = next(reversed(st.plans.values()))
+    n_ops = len(rec.plan)
     if rank == 0:
-        st = engine.state_for(model, device)
-        rec = next(iter(st.plans.values()))
-        line["gpu_launches"] = len(rec.plan) * args.steps
-        line.update(roofline_report(rec.plan, B))
-        if world == 1:
+        line["gpu_launches"] = n_ops * args.steps
+        line.update(roofline_report(rec.plan, B, cfg["flop_per_image"], 3.0 if args.precision == "fp32" else 1.0))
+    if args.precision == "bf16" and not args.no_extras:
+        # the exact-parity mode (bf16x3 split GEMMs, the drop-in default) timed the same way in the same run
+        del model
+        model32 = build_model(args, device, "fp32")
+        ms32 = timed_steps(make_step(model32), args.steps, args.warmup, barrier, world, device)
+        peaks = load_peaks()
+        tf32 = 3.0 * cfg["flop_per_image"] * B / (ms32 * 1e-3) / 1e12
+        line["fp32_mode"] = {"value": world * B / (ms32 / 1e3), "unit": UNIT, "ms_per_step": ms32, "dtype": "bf16x3",
+                             "frac": tf32 / peaks["bf16_sustained"],
+                             "frac_note": "3 x algorithmic FLOPs of the step (three bf16 MMA passes per GEMM) / time / "
+                                          "sustained bf16 peak = fraction of the mode's 1/3-peak bound"}
+        del model32
+    if rank == 0:
+        if world == 1 and not args.no_extras:
+            line["gpu_eager_baseline"] = time_gpu_eager(args, device, B)
             torch.set_num_threads(os.cpu_count() or 1)
-            sd = oracle_state_dict()
-            cpu_val, _ = time_oracle(sd, 16, 4, 1)
+            sd = oracle_state_dict(args)
+            n_img = cfg["cpu_sample"]
+            cpu_val, _ = time_oracle(args, sd, n_img, 4, 1)
             line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-                                    "sample": "16 images x 4 timed forwards (1 warm-up) of the same workload through "
+                                    "sample": f"{n_img} images x 4 timed forwards (1 warm-up) of the same workload through "
                                               "oracle/ (CPU restatement of the reference forward)"}
         print(json.dumps(line), file=JSON_OUT, flush=True)
     if world > 1:
@@ -301,54 +400,74 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one launch from an `ncu --set full` capture (not measured live)
-NCU_TRAFFIC = {
-    "mlp_fused": {"bytes": 137.6e6, "note": "stage-3 launch (M=46656, C=384), profiles/r01_mlp_fused.md: 114.5 MB read "
-                  "+ 23.1 MB written by kernel end; algorithmic 112 MB in + 72 MB out (output still dirty in L2)"},
-}
+def ncu_traffic(kernel, detail):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel at this shape, from the committed
+    `ncu --set full` captures (profiles/ncu_traffic.json, keyed "kernel|shape"); None when that shape was not captured."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None, None
+    with open(path) as f:
+        table = json.load(f)
+    for key, rec in table.items():
+        k, _, shape = key.partition("|")
+        if k == kernel and all(tok in detail.split() for tok in shape.split()):
+            return rec["dram_read_bytes"] + rec["dram_write_bytes"], rec.get("source")
+    return None, None
 
 
-def roofline_report(plan, batch):
+def roofline_report(plan, batch, flop_per_image, passes_per_gemm):
     """Per-kernel device times from an event-separated replay of the recorded step (3 passes, averaged), and the
-    roofline of the dominant kernel family (the tcgen05 GEMM) from its algorithmic FLOPs."""
+    roofline of the dominant kernel family from its algorithmic FLOPs (tensor-bound) or bytes (HBM-bound)."""
     peaks = load_peaks()
-    agg = {}
+    agg, per_launch = {}, {}
     passes = 3
+    details = plan.details()
     for _ in range(passes):
-        for name, ms, flops, nbytes in plan.run_timed():
+        for (name, ms, flops, nbytes), det in zip(plan.run_timed(), details):
             a = agg.setdefault(name, [0.0, 0.0, 0.0, 0])
             a[0] += ms; a[1] += flops; a[2] += nbytes; a[3] += 1
+            pl = per_launch.setdefault((name, det), [0.0, 0])
+            pl[0] += ms; pl[1] += 1
     total_ms = sum(a[0] for a in agg.values()) / passes
     kernels = {}
     for name, (ms, flops, nbytes, n) in agg.items():
         kernels[name] = {"launches_per_step": n // passes, "ms_per_step": ms / passes, "share": ms / passes / total_ms,
                          "tflops": flops / ms / 1e9 if ms > 0 else None, "gbs": nbytes / ms / 1e6 if ms > 0 else None}
     dom = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
-    is_tensor = lambda k: k.startswith("gemm") or k.startswith("mlp_fused")  # tcgen05 kernels
+    is_tensor = lambda k: k.startswith("gemm") or k.startswith("mlp_fused") or k.startswith("conv_")  # tcgen05 kernels
+    # the dominant family's most expensive launch shape: the one the committed ncu capture (traffic) should describe
+    dom_shapes = {d: v[0] for (k, d), v in per_launch.items() if k == dom}
+    dom_detail = max(dom_shapes, key=dom_shapes.get) if dom_shapes else ""
+    traffic, traffic_src = ncu_traffic(dom, dom_detail)
     if kernels[dom]["tflops"] and is_tensor(dom):
         roof = {"kernel": dom, "bound": "tensor", "achieved": kernels[dom]["tflops"], "peak": peaks["bf16_sustained"],
                 "unit": "TFLOP/s", "frac": kernels[dom]["tflops"] / peaks["bf16_sustained"],
-                "traffic": NCU_TRAFFIC.get(dom, {}).get("bytes"), "traffic_note": NCU_TRAFFIC.get(dom, {}).get("note"),
+                "traffic": traffic, "traffic_note": f"per launch at {dom_detail}; {traffic_src}" if traffic else None,
                 "peak_source": peaks["source"] + ", sustained figure (kernel timed inside the step)"}
     else:
         roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": kernels[dom]["gbs"] / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"]}
+                "frac": kernels[dom]["gbs"] / peaks["hbm_gbs"], "traffic": traffic,
+                "traffic_note": f"per launch at {dom_detail}; {traffic_src}" if traffic else None,
+                "peak_source": peaks["source"]}
     hbm, tensor = {}, {}
-    dwk = "dwconv7_stats" if "dwconv7_stats" in kernels else "dwconv7_ln"  # bf16 mode / fp32 mode kernel
-    if dwk in kernels:
+    dws = [k for k in kernels if k.startswith("dwconv7")]
+    if dws:
+        dwk = max(dws, key=lambda k: kernels[k]["ms_per_step"])
         hbm = {"kernel": dwk, "bound": "hbm", "achieved": kernels[dwk]["gbs"],
                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": kernels[dwk]["gbs"] / peaks["hbm_gbs"],
-               "note": "HBM by algorithmic bytes (4 B in + 2 B out per element); 49 fp32 FMAs per element make the "
-                       "FMA pipe the practical bound (tflops in `kernels`, 74 TFLOP/s fp32 peak)"}
+               "ms_per_step": kernels[dwk]["ms_per_step"],
+               "note": "HBM by algorithmic bytes (fp32 in + bf16 plane(s) out per element + LayerNorm partial sums); 49 fp32 "
+                       "FMAs per element make the FMA pipe the practical bound (tflops in `kernels`)"}
     fam = [k for k in agg if is_tensor(k)]
     if fam:
-        # all tcgen05 kernels of the step together (fused CNBlock MLPs + the remaining GEMMs): FLOPs / device time
+        # all tcgen05 kernels of the step together: FLOPs actually issued (x3 passes in fp32 mode) / device time
         f_ms = sum(agg[k][0] for k in fam)
         f_tf = sum(agg[k][1] for k in fam) / f_ms / 1e9
         tensor = {"kernel": "+".join(sorted(fam)), "bound": "tensor", "achieved": f_tf, "peak": peaks["bf16_sustained"],
                   "unit": "TFLOP/s", "frac": f_tf / peaks["bf16_sustained"], "ms_per_step": f_ms / passes}
     return {"roofline": roof, "roofline_hbm_kernel": hbm, "roofline_tensor_kernel": tensor, "kernels": kernels,
-            "step_tflops": FLOP_PER_IMAGE * batch / (total_ms * 1e-3) / 1e12}
+            "step_tflops": passes_per_gemm * flop_per_image * batch / (total_ms * 1e-3) / 1e12,
+            "step_ms_event_separated": total_ms}
 
 
 JSON_OUT = sys.stdout
@@ -366,8 +485,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"],
+                    help="BASELINE.json workload (default cfg2 = configs[1], the one the metric is quoted on)")
+    ap.add_argument("--batch", type=int, default=0, help="images per GPU per step (default: the config's)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the fp32_mode block, the GPU-eager and the CPU baselines (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -18,6 +18,8 @@ SIGNATURES = {
     "cpn_check_device": [],
     "cpn_plan_create": [C.POINTER(_vp)],
     "cpn_plan_run": [_vp, _vp],
+    "cpn_plan_capture": [_vp, _vp],
+    "cpn_plan_has_graph": [_vp],
     "cpn_plan_num_ops": [_vp],
     "cpn_plan_run_timed": [_vp, _vp, C.POINTER(C.c_float), _i],
     "cpn_plan_op_info": [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_double)],

@@ -1,6 +1,6 @@
 // C ABI of libcpnb200.so (see include/cpn_b200.h). Host side only: argument checks, TMA descriptor encoding,
 // kernel selection and launch, and the plan recorder. No torch types, no allocation of user-visible memory.
-#include "../../include/cpn_b200.h"
+#include "api_common.h"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -9,7 +9,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <functional>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -19,7 +21,6 @@
 #endif
 #include "convnext_kernels.cuh"
 #include "dwconv_stats.cuh"
-#include "dwconv_tma.cuh"
 #include "gemm_tcgen05.cuh"
 #include "gemm_tma_epi.cuh"
 #include "eval_kernels.cuh"
@@ -27,7 +28,7 @@
 #include "layout_kernels.cuh"
 #include "mlp_fused.cuh"
 
-namespace {
+namespace cpn_api {
 
 thread_local std::string g_err;
 
@@ -41,14 +42,6 @@ int fail(const char* fmt, ...) {
     return -1;
 }
 
-#define CPN_CUDA(expr)                                                                           \
-    do {                                                                                         \
-        cudaError_t _e = (expr);                                                                 \
-        if (_e != cudaSuccess) return fail("%s: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
-    } while (0)
-
-using Launch = std::function<int(cudaStream_t)>;
-
 // Algorithmic work of the op being submitted (for cpn_plan_run_timed's per-op report); set by each entry point.
 struct OpInfo {
     const char* name = "op";
@@ -57,7 +50,7 @@ struct OpInfo {
     std::string detail;  // shape of this launch, for per-op reports
 };
 thread_local OpInfo g_info;
-void set_info(const char* name, double flops, double bytes, const char* fmt = nullptr, ...) {
+void set_info(const char* name, double flops, double bytes, const char* fmt, ...) {
     g_info.name = name;
     g_info.flops = flops;
     g_info.bytes = bytes;
@@ -71,8 +64,6 @@ void set_info(const char* name, double flops, double bytes, const char* fmt = nu
         g_info.detail = buf;
     }
 }
-
-int submit(cpn_plan* plan, void* stream, Launch fn);
 
 // ------------------------------------------------------------------------------------------------ TMA descriptors
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -110,33 +101,60 @@ int make_tmap(CUtensorMap* m, const void* ptr, long long rows, int K, int box_ro
     return 0;
 }
 
-// fp32 channels-last map [B,H,W,C] as a 4-D tensor (C innermost), box = cb channels x ntok tokens of one row.
-int make_tmap_nhwc_f32(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int cb, int ntok) {
+int make_tmap_tiled(CUtensorMap* m, CUtensorMapDataType dtype, int rank, const void* ptr, const cuuint64_t* dims,
+                    const cuuint64_t* strides_bytes, const cuuint32_t* box, CUtensorMapSwizzle swizzle) {
     EncodeTiledFn enc = get_encode_fn();
     if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
     if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA operand not 16-byte aligned");
-    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
-                          static_cast<cuuint64_t>(B)};
-    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 4, static_cast<cuuint64_t>(W) * C * 4,
-                             static_cast<cuuint64_t>(H) * W * C * 4};
-    cuuint32_t box[4] = {static_cast<cuuint32_t>(cb), static_cast<cuuint32_t>(ntok), 1, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(ptr), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUresult r = enc(m, dtype, static_cast<cuuint32_t>(rank), const_cast<void*>(ptr), dims, strides_bytes, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS)
-        return fail("cuTensorMapEncodeTiled (4-D fp32) failed with CUresult %d (B=%d H=%d W=%d C=%d box=%dx%d)",
-                    static_cast<int>(r), B, H, W, C, cb, ntok);
+    if (r != CUDA_SUCCESS) {
+        return fail("cuTensorMapEncodeTiled (rank %d) failed with CUresult %d (dims %llu %llu %llu %llu, box %u %u %u %u)",
+                    rank, static_cast<int>(r), (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                    (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0), box[0],
+                    rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    }
     return 0;
 }
 
+// Row-major [rows, cols] output (bf16 or fp32) for the TMA epilogue: box = 128 bytes x 32 rows, 128-byte swizzle.
+int make_tmap_out(CUtensorMap* m, const void* ptr, long long rows, int cols, bool bf16) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA output not 16-byte aligned");
+    const int esz = bf16 ? 2 : 4;
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * esz};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail("cuTensorMapEncodeTiled (output) failed with CUresult %d (rows=%lld cols=%d)", static_cast<int>(r),
+                    rows, cols);
+    return 0;
+}
+
+// Per-device caches. The SM count and the opt-in to more than 48 KB of dynamic shared memory belong to a device, and one
+// process may drive several of them (nn.DataParallel runs one thread per device: reference main.py:118).
+constexpr int MAX_DEVICES = 64;
+int cur_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < MAX_DEVICES) ? dev : 0;
+}
+
 int num_sms() {
-    static int n = 0;
+    static std::atomic<int> cache[MAX_DEVICES];
+    const int dev = cur_device();
+    int n = cache[dev].load(std::memory_order_relaxed);
     if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         if (n <= 0) n = 148;
+        cache[dev].store(n, std::memory_order_relaxed);
     }
     return n;
 }
@@ -149,34 +167,10 @@ bool pdl_enabled() {
     static const bool on = [] { const char* e = getenv("CPN_PDL"); return e != nullptr && atoi(e) != 0; }();
     return on;
 }
-template <class... KArgs, class... Args>
-cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster,
-                       Args... args) {
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = grid;
-    cfg.blockDim = block;
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[2];
-    unsigned n = 0;
-    if (cluster > 1) {
-        attr[n].id = cudaLaunchAttributeClusterDimension;
-        attr[n].val.clusterDim.x = cluster;
-        attr[n].val.clusterDim.y = 1;
-        attr[n].val.clusterDim.z = 1;
-        ++n;
-    }
-    if (pdl_enabled()) {
-        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[n].val.programmaticStreamSerializationAllowed = 1;
-        ++n;
-    }
-    cfg.attrs = attr;
-    cfg.numAttrs = n;
-    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
-}
+}  // namespace cpn_api
+using namespace cpn_api;
 
+namespace {
 // ------------------------------------------------------------------------------------------------ GEMM dispatch
 struct GemmLaunch {
     CUtensorMap ta, tb, ta_lo, tb_lo;
@@ -188,11 +182,7 @@ template <int BN, int ACT, bool SPLIT>
 int launch_gemm_inst(const GemmLaunch& g, cudaStream_t st) {
     using S = cpn::GemmSmem<BN, SPLIT>;
     auto kern = cpn::gemm_bf16_tcgen05_kernel<BN, ACT, SPLIT>;
-    static bool attr_done = false;  // per instantiation
-    if (!attr_done) {
-        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-        attr_done = true;
-    }
+    CPN_CUDA(ensure_smem(kern, S::TOTAL));
     kern<<<g.grid, cpn::GEMM_THREADS, S::TOTAL, st>>>(g.ta, g.tb, g.ta_lo, g.tb_lo, g.p);
     CPN_CUDA(cudaGetLastError());
     return 0;
@@ -240,25 +230,6 @@ int pick_bn(int M, int N, bool split) {
     return best;
 }
 
-// Row-major [rows, cols] output (bf16 or fp32) for the TMA epilogue: box = 128 bytes x 32 rows, 128-byte swizzle.
-int make_tmap_out(CUtensorMap* m, const void* ptr, long long rows, int cols, bool bf16) {
-    EncodeTiledFn enc = get_encode_fn();
-    if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
-    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail("TMA output not 16-byte aligned");
-    const int esz = bf16 ? 2 : 4;
-    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
-    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * esz};
-    cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), 32};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS)
-        return fail("cuTensorMapEncodeTiled (output) failed with CUresult %d (rows=%lld cols=%d)", static_cast<int>(r),
-                    rows, cols);
-    return 0;
-}
-
 struct Gemm2Launch {
     CUtensorMap ta, tb, tout;
     cpn::Gemm2Params p;
@@ -270,11 +241,7 @@ template <int BN, int EPI, int CG, int EW = cpn::GEMM_EPI_WARPS>
 int launch_gemm2_inst(const Gemm2Launch& g, cudaStream_t st) {
     using S = cpn::Gemm2Cfg<BN, EPI, CG, EW>;
     auto kern = cpn::gemm_tma_epi_kernel<BN, EPI, CG, EW>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-        attr_done = true;
-    }
+    CPN_CUDA(ensure_smem(kern, S::TOTAL));
     CPN_CUDA(launch_pdl(kern, dim3(g.grid), dim3(S::THREADS), S::TOTAL, st, CG, g.ta, g.tb, g.tout, g.p));
     CPN_CUDA(cudaGetLastError());
     return 0;
@@ -348,8 +315,6 @@ int pick_bn2(int M, int N, int epi) {
     return best;
 }
 
-int make_tmap(CUtensorMap* m, const void* ptr, long long rows, int K, int box_rows);
-
 // Tile geometry of a TMA-epilogue GEMM: CTA pairs (cta_group::2, 256-row tiles, each CTA stages half of the B tile)
 // when the tile is wide enough to split and there is at least one pair tile per SM pair; CPN_GEMM_2SM=0 disables.
 int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, int epi) {
@@ -368,8 +333,12 @@ int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, 
     g.p.num_k_blocks = (K + cpn::GEMM_BK - 1) / cpn::GEMM_BK;
     static const int order = [] { const char* e = getenv("CPN_GEMM_ORDER"); return e == nullptr ? 0 : atoi(e); }();
     g.p.m_fastest = order;
+#ifdef CPN_DEV_KNOBS
     static const int dbg = [] { const char* e = getenv("CPN_GEMM_DBG"); return e == nullptr ? 0 : atoi(e); }();
     g.p.dbg = dbg;
+#else
+    g.p.dbg = 0;
+#endif
     const int tiles = g.p.num_m_blocks * g.p.num_n_blocks;
     const int slots = num_sms() / g.cg;
     g.grid = g.cg * (tiles < slots ? tiles : slots);
@@ -382,9 +351,14 @@ int gemm2_geometry(Gemm2Launch& g, const void* Bw, int M, int N, int K, int bn, 
 struct cpn_plan {
     std::vector<Launch> ops;
     std::vector<OpInfo> info;
+    cudaGraphExec_t exec = nullptr;  // the same launches as one CUDA graph (cpn_plan_capture); replayed by cpn_plan_run
+    size_t captured_ops = 0;
+    ~cpn_plan() {
+        if (exec != nullptr) cudaGraphExecDestroy(exec);
+    }
 };
 
-namespace {
+namespace cpn_api {
 int submit(cpn_plan* plan, void* stream, Launch fn) {
     if (plan != nullptr) {
         plan->ops.push_back(std::move(fn));
@@ -393,87 +367,7 @@ int submit(cpn_plan* plan, void* stream, Launch fn) {
     }
     return fn(static_cast<cudaStream_t>(stream));
 }
-}  // namespace
-
-namespace {
-// Launch geometry of the TMA depthwise kernel: threads per strip (channel pairs rounded up to whole warps), strips
-// per CTA G, tokens per strip TW and row chunks, chosen by a wave-count x rows x TW cost model.
-struct Dw2Geom {
-    bool ok = false;
-    int NT = 192, G = 1, gthreads = 0, TW = 4, chunks = 1, CB = 0, nbox = 1, nst = 4;
-    int box_bytes = 0, stage_bytes = 0;
-    size_t smem = 0;
-};
-
-Dw2Geom dw2_geometry(int B, int H, int W, int C) {
-    Dw2Geom g;
-    const int half = C / 2;
-    if (C % 4 != 0 || half <= 0) return g;
-    g.gthreads = ((half + 31) / 32) * 32;
-    if (g.gthreads <= 192) g.NT = 192;
-    else if (g.gthreads <= 384) g.NT = 384;
-    else return g;
-    g.G = g.NT / g.gthreads;
-    if (g.G > cpn::DW2_MAXG) g.G = cpn::DW2_MAXG;
-    // Round 1: off by default. It is only ahead of the register-marching LDG kernel for C = 384 (profiles/
-    // r01_dwconv_notes.md) and its forward is not yet run-to-run identical there; CPN_DW_TMA=1 enables it.
-    if (getenv("CPN_DW_TMA") == nullptr) return g;
-    g.CB = C;
-    while (g.CB > 256 || C % g.CB != 0 || g.CB % 4 != 0) {
-        --g.CB;
-        if (g.CB < 4) return g;
-    }
-    g.nbox = C / g.CB;
-    const int tw_max = g.NT == 384 ? 2 : 4;  // 384 threads leave 168 registers per thread
-    double best = 1e30;
-    for (int tw = tw_max; tw >= 2; --tw) {
-        for (int chunks = 1; chunks <= 3; ++chunks) {
-            const int cols = g.G * tw;
-            const int strips = (W + cols - 1) / cols;
-            const int rows = (H + chunks - 1) / chunks;
-            const int in_rows = chunks == 1 ? H : rows + 6;
-            const long long ctas = static_cast<long long>(strips) * chunks * B;
-            const long long waves = (ctas + num_sms() - 1) / num_sms();
-            const double cost = static_cast<double>(waves) * (in_rows + 2) * tw * (1.0 + 0.05 * (4 - tw));
-            if (cost < best) { best = cost; g.TW = tw; g.chunks = chunks; }
-        }
-    }
-    const int ntok = g.G * g.TW + 6;
-    if (ntok > 256) return g;
-    g.box_bytes = ((ntok * g.CB * 4 + 127) / 128) * 128;
-    g.stage_bytes = g.nbox * g.box_bytes;
-    const size_t fixed = static_cast<size_t>(cpn::DW2_NSTAT) * cpn::DW2_MAXG * 8 * 4 +
-                         (2 * cpn::DW2_MAX_STAGES + cpn::DW2_NSTAT) * 8 + 128;
-    g.nst = cpn::DW2_MAX_STAGES;
-    while (g.nst > 2 && g.nst * static_cast<size_t>(g.stage_bytes) + fixed > 200 * 1024) --g.nst;
-    g.smem = g.nst * static_cast<size_t>(g.stage_bytes) + fixed;
-    g.ok = g.smem <= 200 * 1024;
-    return g;
-}
-
-template <int TW, int NT>
-int launch_dw2_inst(const CUtensorMap& tm, const cpn::Dw2Params& p, dim3 grid, size_t smem, cudaStream_t st) {
-    auto kern = cpn::dwconv7_ln_tma_kernel<TW, NT>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_done = true;
-    }
-    kern<<<grid, NT, smem, st>>>(tm, p);
-    CPN_CUDA(cudaGetLastError());
-    return 0;
-}
-
-int launch_dw2(int tw, int nt, const CUtensorMap& tm, const cpn::Dw2Params& p, dim3 grid, size_t smem, cudaStream_t st) {
-    if (nt == 384) return launch_dw2_inst<2, 384>(tm, p, grid, smem, st);
-    switch (tw) {
-        case 2: return launch_dw2_inst<2, 192>(tm, p, grid, smem, st);
-        case 3: return launch_dw2_inst<3, 192>(tm, p, grid, smem, st);
-        default: return launch_dw2_inst<4, 192>(tm, p, grid, smem, st);
-    }
-}
-
-}  // namespace
+}  // namespace cpn_api
 
 namespace {
 // Strip width (output columns per lane). A warp's registers live in ONE of the SM's four 16K-register partitions, so
@@ -517,11 +411,7 @@ template <int C, int CG>
 int launch_mlp_inst(const MlpLaunch& g, cudaStream_t st) {
     using S = cpn::MlpCfg<C, CG>;
     auto kern = cpn::mlp_fused_kernel<C, CG>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        CPN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-        attr_done = true;
-    }
+    CPN_CUDA(ensure_smem(kern, S::TOTAL));
     CPN_CUDA(launch_pdl(kern, dim3(g.grid), dim3(S::THREADS), S::TOTAL, st, CG, g.tx, g.tw1, g.tw2, g.p));
     CPN_CUDA(cudaGetLastError());
     return 0;
@@ -557,8 +447,48 @@ int cpn_plan_create(cpn_plan** out) {
     return 0;
 }
 
+int cpn_plan_capture(cpn_plan* plan, void* stream) {
+    if (plan == nullptr) return fail("cpn_plan_capture: null plan");
+    if (plan->ops.empty()) return fail("cpn_plan_capture: empty plan");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (plan->exec != nullptr) {
+        cudaGraphExecDestroy(plan->exec);
+        plan->exec = nullptr;
+    }
+    // ThreadLocal: other host threads (a second device's DataParallel thread, the allocator) are not affected
+    CPN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    int rc = 0;
+    for (auto& op : plan->ops) {
+        rc = op(st);
+        if (rc != 0) break;
+    }
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(st, &graph);
+    if (rc != 0) {
+        if (graph != nullptr) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess || graph == nullptr) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    const cudaError_t ei = cudaGraphInstantiate(&plan->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) {
+        plan->exec = nullptr;
+        return fail("cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+    }
+    plan->captured_ops = plan->ops.size();
+    return 0;
+}
+
+int cpn_plan_has_graph(const cpn_plan* plan) {
+    return plan != nullptr && plan->exec != nullptr && plan->captured_ops == plan->ops.size() ? 1 : 0;
+}
+
 int cpn_plan_run(cpn_plan* plan, void* stream) {
     if (plan == nullptr) return fail("cpn_plan_run: null plan");
+    if (plan->exec != nullptr && plan->captured_ops == plan->ops.size()) {
+        CPN_CUDA(cudaGraphLaunch(plan->exec, static_cast<cudaStream_t>(stream)));
+        return 0;
+    }
     for (auto& op : plan->ops) {
         const int rc = op(static_cast<cudaStream_t>(stream));
         if (rc != 0) return rc;
@@ -624,9 +554,7 @@ int cpn_stem_ln(cpn_plan* plan, const float* x, const float* w, const float* bia
         const long long cap2 = 2LL * num_sms();  // 124 registers x 256 threads: two resident CTAs per SM
         const int grid2 = static_cast<int>(rows < cap2 ? rows : cap2);
         return submit(plan, stream, [=](cudaStream_t st) -> int {
-            if (smem2 > 48 * 1024)
-                CPN_CUDA(cudaFuncSetAttribute(cpn::stem_ln_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              static_cast<int>(smem2)));
+            CPN_CUDA(ensure_smem(cpn::stem_ln_rows_kernel, smem2));
             CPN_CUDA(launch_pdl(cpn::stem_ln_rows_kernel, grid2, dim3(cpn::STEM2_THREADS), smem2, st, 1, x, w, bias, ln_w, ln_b,
                                 out, B, H, W, Ho, Wo, eps));
             CPN_CUDA(cudaGetLastError());
@@ -645,30 +573,6 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
                    void* stream) {
     if (C % 2 != 0 || C > 2 * 32 * cpn::DW_MAX_WARPS) return fail("cpn_dwconv7_ln: unsupported C=%d", C);
     if (B <= 0 || B > 65535) return fail("cpn_dwconv7_ln: unsupported B=%d", B);
-    {
-        const Dw2Geom g = dw2_geometry(B, H, W, C);
-        if (g.ok) {
-            CUtensorMap tm;
-            if (make_tmap_nhwc_f32(&tm, x, B, H, W, C, g.CB, g.G * g.TW + 6) != 0) return -1;
-            cpn::Dw2Params p;
-            p.w49 = w49; p.bias = bias; p.ln_w = ln_w; p.ln_b = ln_b;
-            p.out_hi = static_cast<__nv_bfloat16*>(out_hi);
-            p.out_lo = static_cast<__nv_bfloat16*>(out_lo);
-            p.H = H; p.W = W; p.C = C; p.G = g.G; p.gthreads = g.gthreads; p.CB = g.CB; p.nbox = g.nbox;
-            p.box_bytes = g.box_bytes; p.stage_bytes = g.stage_bytes; p.nst = g.nst;
-            p.rows_per_cta = (H + g.chunks - 1) / g.chunks; p.eps = eps;
-            const int cols = g.G * g.TW;
-            const dim3 grid((W + cols - 1) / cols, (H + p.rows_per_cta - 1) / p.rows_per_cta, B);
-            const size_t smem = g.smem;
-            const int tw = g.TW, nt = g.NT;
-            set_info("dwconv7_ln", 2.0 * 49 * B * H * W * C, 1.0 * B * H * W * C * (4 + 2 + (out_lo != nullptr ? 2 : 0)),
-                     "B=%d H=%d W=%d C=%d tma NT=%d G=%d TW=%d chunks=%d nst=%d", B, H, W, C, g.NT, g.G, g.TW, g.chunks,
-                     g.nst);
-            return submit(plan, stream, [=](cudaStream_t st) -> int {
-                return launch_dw2(tw, nt, tm, p, grid, smem, st);
-            });
-        }
-    }
     const int threads = ((C / 2 + 31) / 32) * 32;
     const int tw = (threads > 192) ? 2 : 4;
     // rows per CTA: whole column strips when the batch already fills the machine, shorter segments otherwise
@@ -772,12 +676,17 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
     static const int stagger_pct = [] { const char* e = getenv("CPN_MLP_STAGGER"); return e == nullptr ? 50 : atoi(e); }();
     const int tile_cycles = C == 384 ? 75000 : C == 192 ? 32000 : 15500;  // measured, profiles/r01_mlp_fused.md
     g.p.stagger = tile_cycles / 100 * stagger_pct;  // negative percentage: delays spread over 0.5 .. 1.44 of it
+#ifdef CPN_DEV_KNOBS
     static const int mlp_dbg = [] { const char* e = getenv("CPN_MLP_DBG"); return e == nullptr ? 0 : atoi(e); }();
     g.p.dbg = mlp_dbg;
+#else
+    g.p.dbg = 0;
+#endif
     const int slots = num_sms() / cg;
     g.grid = cg * (g.p.num_tiles < slots ? g.p.num_tiles : slots);
     const double mc = static_cast<double>(M) * C;
     set_info("mlp_fused", 16.0 * mc * C, 2.0 * mc + 8.0 * mc + 16.0 * C * C, "M=%d C=%d cg=%d", M, C, cg);
+#ifdef CPN_DEV_KNOBS
     static long long* ts_dev = nullptr;  // dev only: CPN_MLP_TS=1 prints a clock64 trace of CTA 0's first tile
     static const bool want_ts = getenv("CPN_MLP_TS") != nullptr;
     if (want_ts && plan == nullptr) {
@@ -785,6 +694,7 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
         CPN_CUDA(cudaMemset(ts_dev, 0, 512 * sizeof(long long)));
         g.p.ts = ts_dev;
     }
+#endif
     auto run = [=](cudaStream_t st) -> int {
         if (cg == 2) {
             switch (C) {
@@ -795,6 +705,7 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
         }
         return C == 96 ? launch_mlp_inst<96, 1>(g, st) : launch_mlp_inst<192, 1>(g, st);
     };
+#ifdef CPN_DEV_KNOBS
     if (g.p.ts != nullptr) {
         if (run(static_cast<cudaStream_t>(stream)) != 0) return -1;
         CPN_CUDA(cudaDeviceSynchronize());
@@ -821,6 +732,7 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
         }
         return 0;
     }
+#endif
     return submit(plan, stream, run);
 }
 
@@ -964,9 +876,7 @@ int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const f
     const int grid = static_cast<int>(blocks);
     set_info("addon_conv1x1", 2.0 * T * C * P, 4.0 * T * (C + P));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        if (smem > 48 * 1024)
-            CPN_CUDA(cudaFuncSetAttribute(cpn::addon_conv1x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          static_cast<int>(smem)));
+        CPN_CUDA(ensure_smem(cpn::addon_conv1x1_kernel, smem));
         cpn::addon_conv1x1_kernel<<<grid, 256, smem, st>>>(feat, w, bias, z, T, C, P);
         CPN_CUDA(cudaGetLastError());
         return 0;
@@ -988,9 +898,7 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
 #define CPN_SMP_CASE(NVV)                                                                                              \
     case NVV:                                                                                                          \
         if (arg) {                                                                                                     \
-            if (smem > 48 * 1024)                                                                                      \
-                CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_reg_kernel<NVV, true>,                                 \
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));   \
+            CPN_CUDA(ensure_smem(cpn::softmax_pool_reg_kernel<NVV, true>, smem));   \
             CPN_CUDA(launch_pdl(cpn::softmax_pool_reg_kernel<NVV, true>, grid, dim3(256), smem, st, 1, z, mode, partial,  \
                                 partial_arg, HW, chunks));                                                            \
         } else {                                                                                                       \
@@ -1009,9 +917,7 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
     }
     int* parg = arg ? partial_arg : nullptr;
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        if (smem > 48 * 1024)
-            CPN_CUDA(cudaFuncSetAttribute(cpn::softmax_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          static_cast<int>(smem)));
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_kernel, smem));
         cpn::softmax_pool_kernel<<<grid, 256, smem, st>>>(z, gumbel, tau, hard, mode, map, partial, parg, HW, P, chunks);
         CPN_CUDA(cudaGetLastError());
         return 0;
@@ -1069,8 +975,7 @@ int cpn_eval_batch(cpn_plan* plan, const float* pooled, const float* out, const 
     set_info("eval_batch", 0.0, 4.0 * B * K * P + 4.0 * B * (P + K) + 2.0 * K * P);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         CPN_CUDA(cudaMemsetAsync(relevant, 0, static_cast<size_t>(K) * P, st));  // per-batch statistic
-        if (P > 48 * 1024)
-            CPN_CUDA(cudaFuncSetAttribute(cpn::eval_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P));
+        CPN_CUDA(ensure_smem(cpn::eval_batch_kernel, P));
         cpn::eval_batch_kernel<<<B, cpn::EVAL_THREADS, static_cast<size_t>(P), st>>>(ep);
         CPN_CUDA(cudaGetLastError());
         cpn::eval_class_count_kernel<<<K, 128, 0, st>>>(relevant, protos_per_class, P);
@@ -1111,9 +1016,7 @@ int cpn_head_tail(cpn_plan* plan, const float* partial, int chunks, int mode, in
     if (D > 4096) ks = 1;                    // dense count encodings are not worth repeating
     set_info("head_tail", 2.0 * B * D * K, 4.0 * B * (1.0 * chunks * P + 1.0 * D * K));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        if (smem > 48 * 1024)
-            CPN_CUDA(cudaFuncSetAttribute(cpn::head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          static_cast<int>(smem)));
+        CPN_CUDA(ensure_smem(cpn::head_tail_kernel, smem));
         CPN_CUDA(launch_pdl(cpn::head_tail_kernel, dim3(B, ks), dim3(256), smem, st, 1, tp));
         CPN_CUDA(cudaGetLastError());
         return 0;

@@ -37,6 +37,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     return d;
 }
 __device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
+__device__ __forceinline__ uint32_t pack2(float a, float b) { return pack_bf16x2(a, b); }
 
 // ------------------------------------------------------------------------------------------------ stem
 // One warp handles 8 horizontally adjacent output tokens; lane l owns output channels l, l+32, l+64.

@@ -40,7 +40,7 @@ struct Gemm2Params {
     // tile order: 0 = consecutive tiles walk the N blocks of one M block (co-running CTAs share the A tile),
     // 1 = consecutive tiles walk the M blocks of one N block (co-running CTAs share the B tile)
     int m_fastest;
-    int dbg;  // timing experiments only (CPN_GEMM_DBG): bit 1 = MMA thread skips the MMAs, bit 2 = epilogue skips its TMA stores
+    int dbg;  // -DCPN_DEV_KNOBS builds only (CPN_GEMM_DBG): bit 1 = MMA thread skips the MMAs, bit 2 = epilogue skips its TMA stores
 };
 
 // CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cluster of two, tcgen05 cta_group::2) per 256 x BN tile;
@@ -180,7 +180,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     const uint64_t bdesc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(stage_b(stage)));
 #pragma unroll
                     for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k) {
-                        if (p.dbg & 2) continue;
+                        if (CPN_DBG(p.dbg, 2)) continue;
                         ptx::umma_bf16_if<CG>(el, tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                     }
                     ptx::umma_commit_if<CG>(el, &empty_bar[stage]);  // frees the stage (in both CTAs of a pair)
@@ -336,7 +336,7 @@ gemm_tma_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 }
                 ptx::fence_proxy_async();  // generic-proxy writes -> visible to the TMA store
                 __syncwarp();
-                if (lane == 0 && !(p.dbg & 4)) {
+                if (lane == 0 && !CPN_DBG(p.dbg, 4)) {
                     ptx::tma_store_2d(&tmap_out, stg_ptr + b * S::STG_BLOCK, col0, row0);
                     ptx::bulk_commit();
                 }

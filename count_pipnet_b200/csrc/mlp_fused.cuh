@@ -30,9 +30,9 @@ struct MlpParams {
     const float* bias2;   // [C]
     const float* scale;   // [C] layer_scale
     float* x;             // [M, C] fp32 residual stream, updated in place
-    long long* ts;        // dev only (CPN_MLP_TS): clock64 trace of CTA 0's first tile, [2][32][8]
+    long long* ts;        // -DCPN_DEV_KNOBS builds only (CPN_MLP_TS): clock64 trace of CTA 0's first tile, [2][32][8]
     int stagger;          // cycles by which CTA groups with one tile less than the others start late (see api.cu)
-    int dbg;              // timing experiments (CPN_MLP_DBG): 1 = E1 skips its math, 2 = no MMAs, 4 = no weight loads
+    int dbg;              // -DCPN_DEV_KNOBS builds only (CPN_MLP_DBG): 1 = E1 skips its math, 2 = no MMAs, 4 = no weight loads
 };
 
 template <int C, int CG>
@@ -163,23 +163,23 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 for (int s = 0; s <= NJ; ++s) {
                     if (s < NJ) {  // W1 rows of chunk s, all k-blocks
                         ptx::mbar_wait(&w_empty[stage], phase ^ 1);
-                        if (p.dbg & 4) { if (rank == 0) ptx::mbar_arrive(&w_full[stage]); }
+                        if (CPN_DBG(p.dbg, 4)) { if (rank == 0) ptx::mbar_arrive(&w_full[stage]); }
                         else if (rank == 0) ptx::mbar_arrive_expect_tx(&w_full[stage], CG * S::W1_BYTES);
                         uint8_t* dst = ws + stage * S::W_STAGE;
 #pragma unroll
                         for (int kb = 0; kb < KB1; ++kb)
-                            if (!(p.dbg & 4)) load(dst + kb * S::W1_KB_BYTES, &tmap_w1, kb * 64, s * 64 + static_cast<int>(rank) * (64 / CG),
+                            if (!(CPN_DBG(p.dbg, 4))) load(dst + kb * S::W1_KB_BYTES, &tmap_w1, kb * 64, s * 64 + static_cast<int>(rank) * (64 / CG),
                                  &w_full[stage]);
                         if (++stage == NW) { stage = 0; phase ^= 1; }
                     }
                     if (s >= 1) {  // W2 k-block of chunk s - 1, all outputs
                         ptx::mbar_wait(&w_empty[stage], phase ^ 1);
-                        if (p.dbg & 4) { if (rank == 0) ptx::mbar_arrive(&w_full[stage]); }
+                        if (CPN_DBG(p.dbg, 4)) { if (rank == 0) ptx::mbar_arrive(&w_full[stage]); }
                         else if (rank == 0) ptx::mbar_arrive_expect_tx(&w_full[stage], CG * S::W2_BYTES);
                         uint8_t* dst = ws + stage * S::W_STAGE;
 #pragma unroll
                         for (int ns = 0; ns < S::NSPLIT; ++ns)
-                            if (!(p.dbg & 4)) load(dst + ns * S::W2_NS_BYTES, &tmap_w2, (s - 1) * 64,
+                            if (!(CPN_DBG(p.dbg, 4))) load(dst + ns * S::W2_NS_BYTES, &tmap_w2, (s - 1) * 64,
                                  ns * S::N2 + static_cast<int>(rank) * (S::N2 / CG), &w_full[stage]);
                         if (++stage == NW) { stage = 0; phase ^= 1; }
                     }
@@ -208,7 +208,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 for (int s = 0; s <= NJ; ++s) {
                     if (s < NJ) {
                         const uint32_t buf = g1 & 1;
-                        const bool trace = p.ts != nullptr && blockIdx.x == 0 && it == (p.dbg >> 8) && s < 32 && lane == 0;
+                        const bool trace = CPN_TRACE(p.ts) && blockIdx.x == 0 && it == (p.dbg >> 8) && s < 32 && lane == 0;
                         long long* tsp = p.ts + 256 + s * 8;
                         if (trace) tsp[0] = clock64();
                         ptx::mbar_wait(&w_full[stage], phase);
@@ -226,7 +226,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                             const int ksteps = (kb == KB1 - 1 && (C % 64) != 0) ? (C % 64) / GEMM_UMMA_K : FULL;
 #pragma unroll
                             for (int k = 0; k < FULL; ++k)
-                                if (k < ksteps && !(p.dbg & 2)) mma(d, adesc + 2 * k, bdesc + 2 * k, idesc1, (kb | k) != 0);
+                                if (k < ksteps && !(CPN_DBG(p.dbg, 2))) mma(d, adesc + 2 * k, bdesc + 2 * k, idesc1, (kb | k) != 0);
                         }
                         commit(&w_empty[stage]);
                         commit(&a1_full[buf]);
@@ -236,7 +236,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                     }
                     if (s >= 1) {
                         const int j = s - 1;
-                        const bool trace = p.ts != nullptr && blockIdx.x == 0 && it == (p.dbg >> 8) && s < 32 && lane == 0;
+                        const bool trace = CPN_TRACE(p.ts) && blockIdx.x == 0 && it == (p.dbg >> 8) && s < 32 && lane == 0;
                         long long* tsp = p.ts + 256 + s * 8;
                         if (trace) tsp[3] = clock64();
                         ptx::mbar_wait(&w_full[stage], phase);
@@ -252,7 +252,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                             const uint64_t bdesc = ptx::make_kmajor_sw128_desc(wbase + ns * S::W2_NS_BYTES);
 #pragma unroll
                             for (int k = 0; k < GEMM_BK / GEMM_UMMA_K; ++k)
-                                if (!(p.dbg & 2)) mma(tmem_base + ns * S::N2, adesc + 2 * k, bdesc + 2 * k, idesc2, (j | k) != 0);
+                                if (!(CPN_DBG(p.dbg, 2))) mma(tmem_base + ns * S::N2, adesc + 2 * k, bdesc + 2 * k, idesc2, (j | k) != 0);
                         }
                         commit(&w_empty[stage]);
                         commit(&h_empty[hslot]);
@@ -301,7 +301,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         int it = 0;
         for (int tile = tile0; tile < p.num_tiles; tile += tile_step, ++it) {
             const int row = row_of(tile);
-            const bool ttrace = p.ts != nullptr && blockIdx.x == 0 && warp == 4 && lane == 0 && it < 8;
+            const bool ttrace = CPN_TRACE(p.ts) && blockIdx.x == 0 && warp == 4 && lane == 0 && it < 8;
             if (ttrace) p.ts[480 + it * 4] = clock64();
             cb_issue(0);
             cb_issue(1);
@@ -323,7 +323,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
             for (int j = 0; j < NJ; ++j, ++g1) {
                 const uint32_t buf = g1 & 1;
                 uint32_t r0[32];
-                const bool trace = p.ts != nullptr && blockIdx.x == 0 && warp == 4 && lane == 0 && it == (p.dbg >> 8) && j < 32;
+                const bool trace = CPN_TRACE(p.ts) && blockIdx.x == 0 && warp == 4 && lane == 0 && it == (p.dbg >> 8) && j < 32;
                 long long* tsp = p.ts + j * 8;
                 if (trace) tsp[0] = clock64();
                 cb_issue(j + 2);
@@ -342,7 +342,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 if (trace) tsp[4] = clock64();
                 const uint32_t dst = ptx::smem_u32(hs + hslot * S::H_SLOT) + row_off;
                 const uint32_t cb = cb_addr + static_cast<uint32_t>(j & 3) * 256;
-                if (p.dbg & 1) {
+                if (CPN_DBG(p.dbg, 1)) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
                         ptx::sts_u4(dst + ((static_cast<uint32_t>(4 * half + i) ^ sw) << 4),

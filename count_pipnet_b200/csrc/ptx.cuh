@@ -7,6 +7,16 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 
+// Work-skipping timing experiments (skip the MMAs, the stores, the weight loads ...) and clock64 traces exist only in a
+// -DCPN_DEV_KNOBS build; in the product library these conditions are compile-time false and the code behind them is gone.
+#ifdef CPN_DEV_KNOBS
+#define CPN_DBG(flags, bit) (((flags) & (bit)) != 0)
+#define CPN_TRACE(ptr) ((ptr) != nullptr)
+#else
+#define CPN_DBG(flags, bit) false
+#define CPN_TRACE(ptr) false
+#endif
+
 namespace cpn {
 namespace ptx {
 

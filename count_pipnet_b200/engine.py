@@ -15,6 +15,7 @@ from __future__ import annotations
 import os
 import threading
 import weakref
+from collections import OrderedDict
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -22,10 +23,17 @@ import torch.nn as nn
 
 from . import _lib, ops
 
-# "bf16": bf16 tensor-core operands, fp32 accumulate/residual (2e-2 parity bar).
-# "fp32": bf16 hi/lo split operands, three MMA passes (1e-4 parity bar).
-DEFAULT_PRECISION = os.environ.get("CPN_PRECISION", "bf16")
+# "fp32" (the drop-in default): bf16 hi/lo split operands, three MMA passes per GEMM -- the mode that meets the north
+#         star's exact rules (predicted class, arg-max prototype and counts equal to the reference's; pooled / logits
+#         within 1e-4) on every parity case.
+# "bf16" (opt-in: `model.cpn_precision = "bf16"` or CPN_PRECISION=bf16): bf16 tensor-core operands, fp32 accumulate and
+#         residual stream; about twice as fast, pooled / logits within 2e-2, and a count or a thresholded score that
+#         sits within that distance of its rounding boundary / the 0.1 threshold may land on the other side.
+DEFAULT_PRECISION = os.environ.get("CPN_PRECISION", "fp32")
 USE_PLANS = os.environ.get("CPN_NO_PLAN", "0") != "1"
+# Replay a recorded plan as one CUDA graph from its second run on (small batches are launch-bound otherwise).
+USE_GRAPHS = os.environ.get("CPN_GRAPHS", "1") != "0"
+MAX_PLANS = 8  # recorded plans kept per (module, device), least recently used dropped first
 
 _LOCK = threading.RLock()
 _STATES: "weakref.WeakKeyDictionary[nn.Module, Dict[int, object]]" = weakref.WeakKeyDictionary()
@@ -59,6 +67,7 @@ class Buffers:
     def __init__(self, device):
         self.device = device
         self.t: Dict[str, torch.Tensor] = {}
+        self.regrown = False  # a buffer that recorded plans may point at has been replaced by a larger one
 
     def get(self, name: str, shape, dtype) -> torch.Tensor:
         n = 1
@@ -66,6 +75,8 @@ class Buffers:
             n *= int(s)
         cur = self.t.get(name)
         if cur is None or cur.dtype != dtype or cur.numel() < n:
+            if cur is not None:
+                self.regrown = True
             cur = torch.empty(max(n, 1), dtype=dtype, device=self.device)
             self.t[name] = cur
         return cur[:n].view(*shape)
@@ -95,10 +106,30 @@ class State:
         self.program = None
         self.packed_sig = None
         self.packed_precision = None
-        self.plans: Dict[tuple, ops.Plan] = {}
+        self.plans: "OrderedDict[tuple, object]" = OrderedDict()
+
+    def remember(self, key, rec) -> None:
+        """Keep `rec` as the most recent plan. Plans recorded against buffers that have since been replaced by larger
+        ones pin the old allocations (Plan.keepalive): when that happened during this recording, drop them; otherwise
+        keep at most MAX_PLANS."""
+        if self.buffers.regrown:
+            self.plans.clear()
+            self.buffers.regrown = False
+        self.plans[key] = rec
+        self.plans.move_to_end(key)
+        while len(self.plans) > MAX_PLANS:
+            self.plans.popitem(last=False)
 
 
 def state_for(module: nn.Module, device: torch.device) -> State:
+    if getattr(module, "_is_replica", False):
+        # nn.DataParallel over several devices (reference main.py:118) builds throw-away replicas with fresh weight
+        # copies on every forward: packed weights, TMA descriptors and plans could never be reused. One device under
+        # DataParallel calls the module itself and is fine.
+        raise _lib.CpnError(
+            "the fused B200 forward keeps per-(module, device) packed weights and launch plans and cannot run inside "
+            "multi-device nn.DataParallel replicas; run one process per GPU (torchrun) and shard the batch with "
+            "count_pipnet_b200.sharding, or pass a single device_id")
     with _LOCK:
         per_dev = _STATES.get(module)
         if per_dev is None:

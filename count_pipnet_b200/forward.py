@@ -133,6 +133,7 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
 class _Recorded:
     def __init__(self, sig, plan, x_in, outs):
         self.sig, self.plan, self.x_in, self.outs = sig, plan, x_in, outs
+        self.runs = 0
 
 
 def _fill_gumbel(noise: Optional[torch.Tensor], model: nn.Module) -> None:
@@ -170,10 +171,17 @@ def network_forward(model: nn.Module, xs: torch.Tensor, inference: bool = False)
                 feat, Hf, Wf, C = prog.emit(em, x_in, B, H, W)
                 outs = _emit_head(em, model, feat, B, Hf, Wf, C, bool(inference), want_map)
                 rec = _Recorded(sig, plan, x_in, outs)
-                st.plans[key] = rec
+                st.remember(key, rec)
+            else:
+                st.plans.move_to_end(key)
             rec.x_in.copy_(x)
             _fill_gumbel(rec.outs["noise"], model)
+            if _e.USE_GRAPHS and rec.runs == 1 and not rec.plan.has_graph:
+                # second forward of this shape: the kernels are loaded and their attributes set, so the launch
+                # sequence can be captured; every later forward is one cudaGraphLaunch
+                rec.plan.capture()
             rec.plan.run()
+            rec.runs += 1
             outs = rec.outs
         else:
             em = Emit(st.buffers, split, None)

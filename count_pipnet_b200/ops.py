@@ -38,6 +38,14 @@ class Plan:
     def run(self) -> None:
         _lib.check(_lib.load().cpn_plan_run(self.handle, _stream()))
 
+    def capture(self) -> None:
+        """Turn the recorded launches into one CUDA graph (captured on torch's current stream); run() replays it."""
+        _lib.check(_lib.load().cpn_plan_capture(self.handle, _stream()))
+
+    @property
+    def has_graph(self) -> bool:
+        return bool(_lib.load().cpn_plan_has_graph(self.handle))
+
     def __len__(self) -> int:
         return _lib.load().cpn_plan_num_ops(self.handle)
 

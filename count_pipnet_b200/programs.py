@@ -158,8 +158,10 @@ class ConvNeXtProgram:
         plan = em.plan
         T = B * H * W
         a_hi, a_lo = em.pair("act", (T, C))
-        h_hi, h_lo = em.pair("hid", (T, 4 * C))
         folded = all("w1g" in pk for _, pk in blocks)
+        fused = folded and FUSED_MLP and C in (96, 192, 384)
+        # the 4C-wide hidden plane exists in HBM only when the MLP runs as two GEMMs
+        h_hi, h_lo = (None, None) if fused else em.pair("hid", (T, 4 * C))
         if not folded:
             for s, pk in blocks:
                 blk = s[1]
@@ -181,7 +183,7 @@ class ConvNeXtProgram:
                 blk = s[1]
                 dw, ln, fc2 = blk.block[0], blk.block[2], blk.block[5]
                 ops.dwconv7_stats(res4[b0:b1], pk["w49"], dw.bias.detach(), a_hi[t0:t1], stats[t0:t1], plan=plan)
-                if FUSED_MLP and C in (96, 192, 384):
+                if fused:
                     # fc1 -> GELU -> fc2 -> layer scale -> residual in one kernel, hidden activations stay on the SM
                     ops.mlp_fused(a_hi[t0:t1], pk["w1g"], pk["w2"], t1 - t0, C, stats[t0:t1], pk["w1g_sum"], pk["b1f"],
                                   fc2.bias.detach(), blk.layer_scale.detach().view(C), res2[t0:t1], eps=ln.eps,

@@ -51,6 +51,12 @@ int cpn_check_device(void);
 /* ---- plans: a recorded sequence of launches with pre-encoded TMA descriptors ------------------------------- */
 int cpn_plan_create(cpn_plan** out);
 int cpn_plan_run(cpn_plan* plan, void* stream);
+/* Capture the recorded launches into one CUDA graph on `stream` (cudaStreamBeginCapture .. cudaGraphInstantiate); from
+ * then on cpn_plan_run replays the graph with one cudaGraphLaunch. For small batches (the reference's visualisation and
+ * attribution callers run B = 1 forwards: util/vis_pipnet.py:208-213, util/interpret_idg.py:168-172) the step is
+ * launch-bound otherwise. Call after the plan has run once eagerly (lazy kernel loading is not capturable). */
+int cpn_plan_capture(cpn_plan* plan, void* stream);
+int cpn_plan_has_graph(const cpn_plan* plan);
 int cpn_plan_num_ops(const cpn_plan* plan);
 /* Replay with a CUDA event between consecutive ops; ms_out[i] = device time of op i (synchronises at the end). */
 int cpn_plan_run_timed(cpn_plan* plan, void* stream, float* ms_out, int n);

@@ -163,3 +163,30 @@ def test_load_reference_checkpoint_prefixes(tmp_path):
         ck.load_reference_checkpoint(cases.build(case, my_pipnet, my_count), {"model_state_dict": broken})
     with pytest.raises(ValueError):
         ck.load_reference_checkpoint(dst, {"epoch": 1})
+
+
+def test_bench_configs_match_parity_cases():
+    """bench.py's workloads (count_pipnet_b200/configs.py) are the BASELINE.json configs the parity cases pin."""
+    import cases
+    from count_pipnet_b200 import configs
+    pairs = {"cfg1": "cfg1_count_shapes_onehot_gumbel", "cfg2": "cfg2_pipnet_convnext26_224",
+             "cfg3": "cfg3_pipnet_resnet50_224", "cfg4": "cfg4_count_bilinear_gumbel",
+             "cfg5": "cfg5_pipnet_convnext26_448_map"}
+    for name, case_name in pairs.items():
+        cfg, case = configs.CONFIGS[name], cases.CASES[case_name]
+        for key in ("model", "classes", "size", "args"):
+            assert cfg[key] == case[key], (name, key)
+        assert cfg.get("max_count", 3) == case.get("max_count", 3)
+        assert configs.oracle_cfg(name) == cases.oracle_cfg(case)
+    assert configs.batch_per_gpu("cfg4", 1) == 64 and configs.batch_per_gpu("cfg4", 4) == 128
+    assert configs.batch_per_gpu("cfg3", 8) == 32 and configs.batch_per_gpu("cfg5", 8) == 16
+
+
+def test_multi_device_dataparallel_replica_is_rejected():
+    """A DataParallel replica (torch marks it `_is_replica`) cannot keep packed weights or plans: clear error."""
+    import torch
+    from count_pipnet_b200 import _lib, engine
+    model, _ = my_pipnet.get_pipnet(10, synth.make_args(use_mid_layers=True, num_stages=2))
+    model._is_replica = True
+    with pytest.raises(_lib.CpnError, match="DataParallel"):
+        engine.state_for(model, torch.device("cuda", 0))

@@ -3,7 +3,8 @@
   (b) the oracle recomputed on this box's CPU on the same seeded weights/inputs.
 
 North-star rules: predicted class, arg-max prototype per image and count values exact; pooled scores and logits
-within 1e-4 relative in fp32 mode and 2e-2 in bf16 mode (relative = max|delta| / max|reference| per tensor)."""
+within 1e-4 relative in fp32 mode and 2e-2 in bf16 mode (relative = max|delta| / max|reference| per tensor). The exact
+rules, including how bf16 mode's boundary flips are bounded instead of excused, are in tests/parity_rules.py."""
 import os
 
 import numpy as np
@@ -18,17 +19,14 @@ from count_pipnet_b200.pipnet import pipnet as my_pipnet
 pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-TOL = {"fp32": 1e-4, "bf16": 2e-2}
-
-
-def rel(a, b):
-    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
-    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-12))
+from parity_rules import TOL, check_outputs, rel  # noqa: E402
 
 
 def run_fused(name, precision, device, materialize=True):
     case = cases.CASES[name]
-    model = cases.build(case, my_pipnet, my_count).to(device)
+    model = cases.build(case, my_pipnet, my_count)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    model = model.to(device)
     model.cpn_precision = precision
     model.materialize_proto_map = materialize
     g = dict(np.load(os.path.join(GOLDEN, name + ".npz")))
@@ -37,55 +35,36 @@ def run_fused(name, precision, device, materialize=True):
     x = cases.inputs(case).to(device)
     with torch.no_grad():
         proto, pooled, out = model(x, inference=case["inference"])
-        proto2, pooled2, out2 = model(x, inference=case["inference"])  # second call replays the recorded plan
+        proto2, pooled2, out2 = model(x, inference=case["inference"])  # second call captures the plan into a CUDA graph
+        proto3, pooled3, out3 = model(x, inference=case["inference"])  # third call replays the graph
     torch.cuda.synchronize()
     assert torch.equal(pooled, pooled2) and torch.equal(out, out2)
-    return case, g, proto, pooled.cpu().numpy(), out.cpu().numpy()
+    assert torch.equal(pooled, pooled3) and torch.equal(out, out3)
+    return case, g, sd, proto, pooled.cpu().numpy(), out.cpu().numpy()
+
+
+def golden_raw(case, g):
+    """The reference's value before the head's discontinuity (inference cases): spatial sum / spatial max of the map."""
+    if not case["inference"]:
+        return None
+    return g["map_sum"] if case["model"] == "count_pipnet" else g["map_max"]
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 @pytest.mark.parametrize("name", list(cases.CASES))
 def test_fused_forward_matches_reference_golden(cuda_device, name, precision):
-    case, g, proto, pooled, out = run_fused(name, precision, cuda_device)
+    """Every parity case against the real reference's outputs under tests/parity_rules.py: fp32 mode exact on every image
+    (class, arg-max prototype, counts) and within 1e-4; bf16 mode within 2e-2 with boundary flips counted and bounded and
+    the predicted class required on every image whose (flip-adjusted) top-2 margin exceeds the tolerance."""
+    case, g, sd, proto, pooled, out = run_fused(name, precision, cuda_device)
     tol = TOL[precision]
     assert tuple(proto.shape) == tuple(int(v) for v in g["map_shape"])
-    errs = dict(pooled=rel(pooled, g["pooled"]), out=rel(out, g["out"]))
+    stats = check_outputs(case, sd, precision, pooled, out, g["pooled"], g["out"], golden_raw(case, g))
     flat = proto.reshape(proto.shape[0], proto.shape[1], -1)
-    errs["map_max"] = rel(flat.amax(2).cpu().numpy(), g["map_max"])
-    print(f"{name} [{precision}] " + " ".join(f"{k}={v:.2e}" for k, v in errs.items()))
-    is_count_inf = case["model"] == "count_pipnet" and case["inference"]
-    if is_count_inf and precision == "fp32":
-        # counts are integers: exact or wrong
-        assert np.array_equal(pooled, g["pooled"]), (pooled - g["pooled"]).nonzero()
-    elif is_count_inf:
-        # bf16 mode: a count is round(sum of patch probabilities); it may only differ from the reference where the
-        # reference's raw sum (golden map_sum) sits within the bf16-mode tolerance of a rounding boundary
-        raw = np.clip(g["map_sum"], 0, case["max_count"] + 0.49)
-        near_boundary = np.abs(raw - np.floor(raw) - 0.5) <= tol * np.maximum(1.0, raw)
-        bad = (pooled != g["pooled"]) & ~near_boundary
-        assert not bad.any(), np.argwhere(bad)
-        assert (pooled != g["pooled"]).mean() <= 0.02
-    elif case["model"] == "pipnet" and case["inference"]:
-        # pooled = where(max < 0.1, 0, max) (pipnet/pipnet.py:36) is discontinuous at 0.1: a score whose reference
-        # maximum (golden map_max) lies within the tolerance of the threshold may land on either side of it; there
-        # the un-thresholded value must still match. Everywhere else the thresholded values are compared.
-        scale = np.abs(g["pooled"]).max()
-        near = np.abs(g["map_max"] - 0.1) <= tol * scale
-        assert near.mean() <= 0.1
-        raw = np.where(pooled == 0.0, g["map_max"], pooled)  # what the kernel saw before the threshold, if it kept it
-        assert np.abs(np.where(near, raw - g["map_max"], pooled - g["pooled"])).max() <= tol * scale, errs
-    else:
-        assert errs["pooled"] <= tol, errs
-    # images whose counts / thresholded scores legitimately flipped (bf16 mode, see above) have different logits
-    same = np.ones(out.shape[0], dtype=bool)
-    if precision == "bf16" and case["inference"]:
-        flipped = (pooled != g["pooled"]) & ((pooled == 0) | (g["pooled"] == 0) | is_count_inf)
-        assert flipped.mean() <= 0.01  # the boundary checks above already bound where a flip may happen
-        same = ~flipped.any(axis=1)
-    if same.any():
-        assert rel(out[same], g["out"][same]) <= tol, errs
-        assert np.array_equal(out.argmax(1)[same], g["pred"][same])
-        assert np.array_equal(pooled.argmax(1)[same], g["top_proto"][same])
+    stats["map_max"] = rel(flat.amax(2).cpu().numpy(), g["map_max"])
+    print(f"{name} [{precision}] " + " ".join(f"{k}={v:.2e}" if isinstance(v, float) else f"{k}={v}" for k, v in stats.items()))
+    if not (case["args"].get("activation") == "gumbel_softmax"):
+        assert stats["map_max"] <= tol, stats  # hard Gumbel maps are one-hot: covered by the exact counts
     if precision == "fp32":
         # per-(image, prototype) arg-max patch, where the maximum is not a near-tie
         am = flat.argmax(2).cpu().numpy()
@@ -94,13 +73,36 @@ def test_fused_forward_matches_reference_golden(cuda_device, name, precision):
         assert np.array_equal(am[clear], g["map_argmax"][clear])
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_benchmark_shape_forward_matches_live_oracle(cuda_device, precision):
+    """The benchmark's own forward -- cfg2 at B = 64, map not materialised (183 CTA-pair tiles on 74 pairs, ragged last
+    tiles, staggered starts, 3 pooling CTAs per SM) -- against the oracle recomputed on this box's host cores on the same
+    64 seeded images, under the same rules as the golden cases."""
+    case = dict(cases.CASES["cfg2_pipnet_convnext26_224"], batch=64)
+    model = cases.build(case, my_pipnet, my_count)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    x = cases.inputs(case)
+    torch.set_num_threads(os.cpu_count() or 1)
+    o_proto, o_pooled, o_out = oracle.forward(sd, cases.oracle_cfg(case), x, inference=True)
+    raw = o_proto.amax(dim=(2, 3)).numpy()
+    model = model.to(cuda_device)
+    model.cpn_precision = precision
+    model.materialize_proto_map = False
+    with torch.no_grad():
+        for _ in range(3):  # eager, capture, graph replay
+            none, pooled, out = model(x.to(cuda_device), inference=True)
+    torch.cuda.synchronize()
+    assert none is None
+    stats = check_outputs(case, sd, precision, pooled.cpu().numpy(), out.cpu().numpy(), o_pooled.numpy(), o_out.numpy(), raw)
+    print(f"cfg2 B=64 [{precision}] " + " ".join(f"{k}={v:.2e}" if isinstance(v, float) else f"{k}={v}" for k, v in stats.items()))
+    assert stats["class_checked"] >= 0.9 * 64  # the margin rule must not make the class check vacuous
+
+
 @pytest.mark.parametrize("name", ["cfg2_pipnet_convnext26_224", "cfg1_count_shapes_onehot_gumbel"])
 def test_fused_forward_matches_live_oracle_and_skips_map(cuda_device, name):
     """Same comparison against the oracle recomputed here, with the map not materialised (the benchmark setting)."""
-    case, g, proto, pooled, out = run_fused(name, "fp32", cuda_device, materialize=False)
+    case, g, sd, proto, pooled, out = run_fused(name, "fp32", cuda_device, materialize=False)
     assert proto is None
-    model = cases.build(case, my_pipnet, my_count)
-    sd = {k: v.detach() for k, v in model.state_dict().items()}
     noise = None
     if case["args"].get("activation") == "gumbel_softmax":
         noise = cases.gumbel_noise(tuple(int(v) for v in g["map_shape"]))
