@@ -27,6 +27,8 @@ SIGNATURES = {
     "cpn_stem_ln": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp],
     "cpn_dwconv7_ln": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp],
     "cpn_dwconv7_stats": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "cpn_dwconv7_stats_split": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "cpn_gemm_ln_gelu_split": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp],
     "cpn_mlp_fused": [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp],
     "cpn_gemm_ln_gelu": [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _f, _vp, _vp],
     "cpn_ln_im2col2": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],

@@ -594,8 +594,12 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
     });
 }
 
-int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
-                      float* stats, int B, int H, int W, int C, void* stream) {
+}  // extern "C"
+
+// First-generation kernel (taps in registers, 8 warps per SM); cpn_dwconv7_stats (api_dwconv.cu) selects it with
+// CPN_DW_V1=1 for A/B measurements.
+int cpn_api::dwconv7_stats_v1(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
+                              float* stats, int B, int H, int W, int C, void* stream) {
     if (C != 96 && C != 192 && C != 384 && C != 768)
         return fail("cpn_dwconv7_stats: C=%d is not a ConvNeXt-tiny width (96, 192, 384, 768)", C);
     if (B <= 0 || B > 65535 || H <= 0 || W <= 0) return fail("cpn_dwconv7_stats: bad shape B=%d H=%d W=%d", B, H, W);
@@ -624,6 +628,8 @@ int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const fl
         }
     });
 }
+
+extern "C" {
 
 int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N, int K, const float* stats,
                      int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream) {
@@ -824,6 +830,16 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
                      obf ? "gelu_bf16" : (epi == cpn::EPI_SCALE_RES_F32 ? "scale_res_f32" : "bias_f32"));
             return submit(plan, stream, [=](cudaStream_t st) -> int { return launch_gemm2(g, bn2, epi, st); });
         }
+    }
+    if (split && bias != nullptr && out_bf16 == nullptr && out_f32 != nullptr && res_bf16 == nullptr && !relu_after_res &&
+        act == CPN_ACT_NONE && getenv("CPN_GEMM_LEGACY") == nullptr) {
+        // fp32 mode, fp32 output: three-pass kernel with the TMA epilogue (api_gemm_split.cu)
+        int epi = -1;
+        if (scale != nullptr && res_f32 == out_f32) epi = cpn::EPI_SCALE_RES_F32;
+        else if (scale == nullptr && res_f32 == nullptr) epi = cpn::EPI_BIAS_F32;
+        if (epi >= 0 && gemm_split_supported(N, K, epi))
+            return gemm_split(plan, epi, A, A_lo, Bw, Bw_lo, M, N, K, bias, scale, nullptr, 0, nullptr, 0.f, out_f32, nullptr,
+                              stream);
     }
     const int bn = pick_bn(M, N, split);
     if (bn == 0) return fail("cpn_gemm_bf16: no tile width divides N=%d", N);

@@ -5,39 +5,9 @@
 // Reference arithmetic: torchvision/models/convnext.py:31-36 (LayerNorm2d), :51-57 (CNBlock head), :120-131 (stem),
 // :146-150 (downsample); stride surgery features/convnext_features.py:5-15.
 #pragma once
-#include "ptx.cuh"
+#include "device_utils.cuh"
 
 namespace cpn {
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-}
-
-// Packed fp32x2 FMA (FFMA2 on sm_100a): d = a * b + c on both halves.
-__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
-    unsigned long long ra, rb, rc, rd;
-    ra = *reinterpret_cast<unsigned long long*>(&a);
-    rb = *reinterpret_cast<unsigned long long*>(&b);
-    rc = *reinterpret_cast<unsigned long long*>(&c);
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
-    return *reinterpret_cast<float2*>(&rd);
-}
-
-// bf16(a) in the low half, bf16(b) in the high half (round to nearest even): one F2FP instead of two F2F + shift/or.
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-    uint32_t d;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
-    return d;
-}
-__device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
-__device__ __forceinline__ uint32_t pack2(float a, float b) { return pack_bf16x2(a, b); }
 
 // ------------------------------------------------------------------------------------------------ stem
 // One warp handles 8 horizontally adjacent output tokens; lane l owns output channels l, l+32, l+64.

@@ -3,7 +3,7 @@
 // Maximum absolute error 4.2e-5 (tools/fit_gelu.py), two orders of magnitude below the bf16 rounding of the result
 // that follows. fp32 mode keeps erff (gemm_tcgen05.cuh).
 #pragma once
-#include "convnext_kernels.cuh"
+#include "device_utils.cuh"
 
 namespace cpn {
 

@@ -106,6 +106,21 @@ def dwconv7_stats(x, w49, b, out, stats, plan=None):
     _lib.call("cpn_dwconv7_stats", _ph(plan), ptr(x), ptr(w49), ptr(b), ptr(out), ptr(stats), B, H, W, Cc, _stream())
 
 
+def dwconv7_stats_split(x, w49, b, out_hi, out_lo, stats, plan=None):
+    """fp32 mode: out_hi + out_lo [B*H*W, C] bf16 planes of conv + bias, stats of hi + lo per 32-channel group."""
+    _need_cuda(x, w49, b, out_hi, out_lo, stats)
+    B, H, W, Cc = x.shape
+    _lib.call("cpn_dwconv7_stats_split", _ph(plan), ptr(x), ptr(w49), ptr(b), ptr(out_hi), ptr(out_lo), ptr(stats), B, H,
+              W, Cc, _stream())
+
+
+def gemm_ln_gelu_split(a_hi, a_lo, bw_hi, bw_lo, M, N, K, stats, nparts, colsum, bias, out_hi, out_lo, eps=1e-6, plan=None):
+    """fp32 mode of gemm_ln_gelu: hi/lo operand planes, exact GELU, hi/lo output planes."""
+    _need_cuda(a_hi, a_lo, bw_hi, bw_lo, stats, colsum, bias, out_hi, out_lo)
+    _lib.call("cpn_gemm_ln_gelu_split", _ph(plan), ptr(a_hi), ptr(a_lo), ptr(bw_hi), ptr(bw_lo), M, N, K, ptr(stats),
+              nparts, ptr(colsum), ptr(bias), float(eps), ptr(out_hi), ptr(out_lo), _stream())
+
+
 def gemm_ln_gelu(a, bw, M, N, K, stats, nparts, colsum, bias, out_bf16, eps=1e-6, plan=None):
     """out = gelu(LayerNorm-folded fc1): see cpn_gemm_ln_gelu in include/cpn_b200.h."""
     _need_cuda(a, bw, stats, colsum, bias, out_bf16)

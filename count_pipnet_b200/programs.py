@@ -21,6 +21,8 @@ from .features import resnet_features as rsn
 # lose more to wave quantisation than the HBM round trips cost - so it is off unless CPN_L2_CHUNK_MB is set.
 # CPN_FUSED_MLP=0 falls back to the two-GEMM MLP (fc1 + LN/GELU epilogue, fc2 + scale/residual epilogue)
 FUSED_MLP = os.environ.get("CPN_FUSED_MLP", "1") != "0"
+# CPN_FP32_LEGACY=1: fp32 mode as in round 1 (LayerNorm inside the depthwise kernel, direct-store GEMM epilogues); A/B only
+LEGACY_FP32 = os.environ.get("CPN_FP32_LEGACY", "0") == "1"
 L2_CHUNK_BYTES = float(os.environ.get("CPN_L2_CHUNK_MB", "0")) * 2 ** 20 or 1e18
 
 
@@ -90,15 +92,19 @@ class ConvNeXtProgram:
                     dw, fc1, fc2 = blk.block[0], blk.block[3], blk.block[5]
                     c = dw.out_channels
                     d["w49"] = dw.weight.detach().reshape(c, 49).t().contiguous()
-                    d["w1"], d["w1_lo"] = _split(fc1.weight.detach(), split)
-                    if not split and c in (96, 192, 384, 768):
-                        # bf16 mode: LayerNorm folded into fc1 (csrc/gemm_tma_epi.cuh, EPI_LN_GELU_BF16):
-                        #   fc1(LN(y)) = rstd * (y @ (W1*gamma)^T - mean * rowsum(W1*gamma)) + (b1 + W1 @ beta)
-                        ln = blk.block[2]
-                        w1 = fc1.weight.detach().float()
-                        d["w1g"] = (w1 * ln.weight.detach().float()[None, :]).to(torch.bfloat16).contiguous()
-                        d["w1g_sum"] = d["w1g"].float().sum(1).contiguous()
-                        d["b1f"] = (fc1.bias.detach().float() + w1 @ ln.bias.detach().float()).contiguous()
+                    # LayerNorm folded into fc1 (csrc/gemm_tma_epi.cuh EPI_LN_GELU_BF16, csrc/gemm_split_epi.cuh):
+                    #   fc1(LN(y)) = rstd * (y @ (W1*gamma)^T - mean * rowsum(W1*gamma)) + (b1 + W1 @ beta)
+                    # with (W1*gamma) rounded to bf16 (bf16 mode) or kept as hi + lo planes (fp32 mode); the row sums are
+                    # those of the values the GEMM multiplies with.
+                    ln = blk.block[2]
+                    w1 = fc1.weight.detach().float()
+                    if c % 32 == 0 and not LEGACY_FP32:
+                        d["w1g"], d["w1g_lo"] = _split(w1 * ln.weight.detach().float()[None, :], split)
+                        wsum = d["w1g"].double() if not split else d["w1g"].double() + d["w1g_lo"].double()
+                        d["w1g_sum"] = wsum.sum(1).float().contiguous()
+                        d["b1f"] = (fc1.bias.detach().double() + w1.double() @ ln.bias.detach().double()).float().contiguous()
+                    else:
+                        d["w1"], d["w1_lo"] = _split(fc1.weight.detach(), split)
                     d["w2"], d["w2_lo"] = _split(fc2.weight.detach(), split)
                 elif s[0] == "down":
                     conv = s[2]
@@ -159,7 +165,7 @@ class ConvNeXtProgram:
         T = B * H * W
         a_hi, a_lo = em.pair("act", (T, C))
         folded = all("w1g" in pk for _, pk in blocks)
-        fused = folded and FUSED_MLP and C in (96, 192, 384)
+        fused = folded and not em.split and FUSED_MLP and C in (96, 192, 384)
         # the 4C-wide hidden plane exists in HBM only when the MLP runs as two GEMMs
         h_hi, h_lo = (None, None) if fused else em.pair("hid", (T, 4 * C))
         if not folded:
@@ -174,6 +180,18 @@ class ConvNeXtProgram:
                               scale=blk.layer_scale.detach().view(C), res_f32=res, out_f32=res, plan=plan)
             return
         stats = em.buf("ln_stats", (T, C // 32, 2), torch.float32)
+        if em.split:
+            # fp32 mode: hi/lo planes everywhere, three MMA passes per GEMM (csrc/gemm_split_epi.cuh)
+            res4, res2 = res.view(B, H, W, C), res.view(T, C)
+            for s, pk in blocks:
+                blk = s[1]
+                dw, ln, fc2 = blk.block[0], blk.block[2], blk.block[5]
+                ops.dwconv7_stats_split(res4, pk["w49"], dw.bias.detach(), a_hi, a_lo, stats, plan=plan)
+                ops.gemm_ln_gelu_split(a_hi, a_lo, pk["w1g"], pk["w1g_lo"], T, 4 * C, C, stats, C // 32, pk["w1g_sum"],
+                                       pk["b1f"], h_hi, h_lo, eps=ln.eps, plan=plan)
+                ops.gemm_bf16(h_hi, pk["w2"], T, C, 4 * C, a_lo=h_lo, bw_lo=pk["w2_lo"], bias=fc2.bias.detach(),
+                              scale=blk.layer_scale.detach().view(C), res_f32=res2, out_f32=res2, plan=plan)
+            return
         nb = max(1, min(B, int(L2_CHUNK_BYTES // (16 * H * W * C))))
         res4, res2 = res.view(B, H, W, C), res.view(T, C)
         for b0 in range(0, B, nb):

@@ -82,14 +82,24 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
  * UN-normalised result and per-token partial LayerNorm sums, and the LayerNorm is folded into the fc1 GEMM.
  * cpn_dwconv7_stats: x [B,H,W,C] fp32, w49 [49,C], bias [C]  ->  out [B*H*W, C] bf16 = round(conv + bias),
  *   stats [B*H*W, C/32, 2] fp32 = (sum, sum of squares) of the rounded values over each 32-channel group.
- *   C must be 96, 192, 384 or 768.
+ *   C must be a multiple of 32.
+ * cpn_dwconv7_stats_split (fp32 mode): the same with the value kept to 16 mantissa bits as two planes,
+ *   out_hi = bf16(v), out_lo = bf16(v - out_hi); stats are those of hi + lo (what the three-pass GEMM sees).
  * cpn_gemm_ln_gelu: out[M,N] bf16 = gelu(rstd_m * (A[M,K] * Bw[N,K]^T - mean_m * colsum[n]) + bias[n]) with
  *   Bw = bf16(W1 * ln_weight), colsum[n] = sum_k Bw[n,k], bias = b1 + W1 * ln_bias, and mean_m / rstd_m rebuilt from
  *   stats [M, nparts, 2] (K = C channels per token) -- equals gelu(fc1(LayerNorm(A))) of convnext.py:53-56. */
 int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
                       float* stats, int B, int H, int W, int C, void* stream);
+int cpn_dwconv7_stats_split(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_hi,
+                            void* out_lo, float* stats, int B, int H, int W, int C, void* stream);
 int cpn_gemm_ln_gelu(cpn_plan* plan, const void* A, const void* Bw, int M, int N, int K, const float* stats,
                      int nparts, const float* colsum, const float* bias, float eps, void* out_bf16, void* stream);
+/* fp32 mode of cpn_gemm_ln_gelu: every operand is a (hi, lo) pair of bf16 planes, three MMA passes per k-step
+ * (hi*hi + hi*lo + lo*hi), the GELU is the exact erf form and the result is written as (out_hi, out_lo) planes.
+ * colsum[n] = sum_k (Bw_hi + Bw_lo)[n,k]; stats from cpn_dwconv7_stats_split. N must be a multiple of 128. */
+int cpn_gemm_ln_gelu_split(cpn_plan* plan, const void* A_hi, const void* A_lo, const void* Bw_hi, const void* Bw_lo,
+                           int M, int N, int K, const float* stats, int nparts, const float* colsum, const float* bias,
+                           float eps, void* out_hi, void* out_lo, void* stream);
 
 /* Whole CNBlock MLP in one kernel (bf16 mode; torchvision convnext.py:53-57, 64-66):
  *   x[M,C] += scale * (gelu(rstd_m * (y * w1g^T - mean_m * colsum) + bias1) * w2^T + bias2)

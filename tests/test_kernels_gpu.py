@@ -127,8 +127,15 @@ def test_dwconv7_ln(cuda_device, B, H, W, C):
     assert ((out.float() + lo.float()) - ref).abs().max().item() < 5e-4
 
 
-@pytest.mark.parametrize("B,H,W,C", [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192),
-                                     (1, 56, 56, 96), (2, 3, 2, 96), (1, 1, 1, 384), (1, 54, 54, 768)])
+DW_SHAPES = [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 768), (1, 5, 9, 192), (1, 56, 56, 96),
+             (2, 3, 2, 96), (1, 1, 1, 384), (1, 54, 54, 768),
+             # second-generation kernel: odd image count with two images per job, column blocks (W > 56), several
+             # images per job on narrow maps, the benchmark's own shapes
+             (3, 27, 27, 384), (1, 112, 112, 96), (2, 55, 55, 384), (5, 6, 6, 192), (9, 13, 13, 96), (7, 24, 24, 192),
+             (64, 27, 27, 384), (64, 56, 56, 96), (16, 26, 26, 768)]
+
+
+@pytest.mark.parametrize("B,H,W,C", DW_SHAPES)
 def test_dwconv7_stats(cuda_device, B, H, W, C):
     """Un-normalised depthwise conv (bf16) + per-32-channel partial LayerNorm sums, vs F.conv2d in fp32."""
     g = torch.Generator().manual_seed(C + H)
@@ -151,6 +158,86 @@ def test_dwconv7_stats(cuda_device, B, H, W, C):
     o = out.float().reshape(T, C // 32, 32)
     assert torch.allclose(stats[..., 0], o.sum(-1), rtol=1e-5, atol=1e-4)
     assert torch.allclose(stats[..., 1], (o * o).sum(-1), rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("B,H,W,C", DW_SHAPES[:14])
+def test_dwconv7_stats_split(cuda_device, B, H, W, C):
+    """fp32 mode: hi + lo planes carry conv + bias to ~2^-17; the partial sums are those of hi + lo."""
+    g = torch.Generator().manual_seed(C + H)
+    x = torch.randn(B, H, W, C, generator=g).to(cuda_device)
+    w = (torch.randn(C, 1, 7, 7, generator=g) * 0.2).to(cuda_device)
+    b = torch.randn(C, generator=g).to(cuda_device)
+    T = B * H * W
+    hi = torch.full((T, C), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    lo = torch.full((T, C), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    stats = torch.full((T, C // 32, 2), float("nan"), device=cuda_device)
+    w49 = w.reshape(C, 49).t().contiguous()
+    ops.dwconv7_stats_split(x, w49, b, hi, lo, stats)
+    hi2, lo2, stats2 = torch.empty_like(hi), torch.empty_like(lo), torch.empty_like(stats)
+    ops.dwconv7_stats_split(x, w49, b, hi2, lo2, stats2)
+    ref = F.conv2d(x.double().permute(0, 3, 1, 2), w.double(), b.double(), padding=3, groups=C).permute(0, 2, 3, 1)
+    ref = ref.reshape(T, C)
+    torch.cuda.synchronize()
+    assert torch.equal(hi, hi2) and torch.equal(lo, lo2) and torch.equal(stats, stats2)  # fixed summation order
+    v = hi.float() + lo.float()
+    assert (v.double() - ref).abs().max().item() <= 3e-5 * max(1.0, ref.abs().max().item())
+    o = v.reshape(T, C // 32, 32)
+    assert torch.allclose(stats[..., 0], o.sum(-1), rtol=1e-5, atol=1e-4)
+    assert torch.allclose(stats[..., 1], (o * o).sum(-1), rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (1300, 768), (128, 96), (46656, 384), (20000, 96)])
+def test_gemm_ln_gelu_split(cuda_device, M, C):
+    """fp32 mode: LayerNorm folded into the three-pass fc1 with the exact GELU, hi/lo output planes, vs fp64."""
+    g = torch.Generator().manual_seed(C + 1)
+    N = 4 * C
+    a = (torch.randn(M, C, generator=g) * 1.5 + 0.7).to(cuda_device)
+    w1 = (torch.randn(N, C, generator=g) / C ** 0.5).to(cuda_device)
+    b1 = torch.randn(N, generator=g).to(cuda_device)
+    gamma = (torch.rand(C, generator=g) + 0.5).to(cuda_device)
+    beta = torch.randn(C, generator=g).to(cuda_device)
+    a_hi, a_lo = _bf16_split(a)
+    av = (a_hi.float() + a_lo.float()).reshape(M, C // 32, 32)
+    stats = torch.stack([av.sum(-1), (av * av).sum(-1)], dim=-1).contiguous()
+    w_hi, w_lo = _bf16_split(w1 * gamma[None, :])
+    colsum = (w_hi.double() + w_lo.double()).sum(1).float().contiguous()
+    b1f = (b1.double() + w1.double() @ beta.double()).float().contiguous()
+    o_hi = torch.full((M, N), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    o_lo = torch.full((M, N), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    ops.gemm_ln_gelu_split(a_hi, a_lo, w_hi, w_lo, M, N, C, stats, C // 32, colsum, b1f, o_hi, o_lo)
+    ref = F.gelu(F.linear(F.layer_norm(a.double(), (C,), gamma.double(), beta.double(), 1e-6), w1.double(), b1.double()))
+    torch.cuda.synchronize()
+    out = o_hi.double() + o_lo.double()
+    rel = (out - ref).abs().max().item() / ref.abs().max().item()
+    assert rel < 5e-5, rel
+    # the planes are a proper split: lo is the rounding remainder of hi
+    assert (o_lo.float().abs() <= o_hi.float().abs() * 2.0 ** -8 + 1e-30).all()
+
+
+@pytest.mark.parametrize("M,N,K,res", [(2500, 192, 768, True), (5000, 96, 384, True), (1111, 384, 1536, True),
+                                       (900, 768, 3072, True), (20000, 768, 1536, False), (20000, 384, 768, False),
+                                       (30000, 192, 384, False), (46656, 384, 1536, True)])
+def test_gemm_split_tma_epilogues(cuda_device, M, N, K, res):
+    """fp32 mode, fp32 outputs through the TMA epilogue: x += scale * (h @ W2^T + b) in place, and plain bias (downsample)."""
+    g = torch.Generator().manual_seed(N + K)
+    a = torch.randn(M, K, generator=g).to(cuda_device)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(cuda_device)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    a_hi, a_lo = _bf16_split(a)
+    w_hi, w_lo = _bf16_split(w)
+    ref = a.double() @ w.double().t() + bias.double()
+    if res:
+        x = torch.randn(M, N, generator=g).to(cuda_device)
+        scale = (torch.rand(N, generator=g) + 0.25).to(cuda_device)
+        ref = x.double() + scale.double() * ref
+        ops.gemm_bf16(a_hi, w_hi, M, N, K, a_lo=a_lo, bw_lo=w_lo, bias=bias, scale=scale, res_f32=x, out_f32=x)
+        out = x
+    else:
+        out = torch.full((M, N), float("nan"), device=cuda_device)
+        ops.gemm_bf16(a_hi, w_hi, M, N, K, a_lo=a_lo, bw_lo=w_lo, bias=bias, out_f32=out)
+    torch.cuda.synchronize()
+    rel = (out.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert rel < 5e-5, rel
 
 
 @pytest.mark.parametrize("M,C", [(3000, 192), (777, 96), (2500, 384), (1300, 768), (128, 96)])
