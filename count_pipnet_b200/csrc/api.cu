@@ -450,29 +450,42 @@ int cpn_plan_create(cpn_plan** out) {
 int cpn_plan_capture(cpn_plan* plan, void* stream) {
     if (plan == nullptr) return fail("cpn_plan_capture: null plan");
     if (plan->ops.empty()) return fail("cpn_plan_capture: empty plan");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    (void)stream;  // the capture only records: it runs on a private stream (torch's default stream is the legacy stream,
+                   // which cannot be captured) and the graph is later launched into whatever stream cpn_plan_run is given
     if (plan->exec != nullptr) {
         cudaGraphExecDestroy(plan->exec);
         plan->exec = nullptr;
     }
+    cudaStream_t st = nullptr;
+    CPN_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     // ThreadLocal: other host threads (a second device's DataParallel thread, the allocator) are not affected
-    CPN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    cudaError_t e = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) {
+        cudaStreamDestroy(st);
+        return fail("cudaStreamBeginCapture: %s", cudaGetErrorString(e));
+    }
     int rc = 0;
     for (auto& op : plan->ops) {
         rc = op(st);
         if (rc != 0) break;
     }
     cudaGraph_t graph = nullptr;
-    const cudaError_t e = cudaStreamEndCapture(st, &graph);
+    e = cudaStreamEndCapture(st, &graph);  // always: leaves the stream out of capture mode, also after a failed op
+    cudaStreamDestroy(st);
     if (rc != 0) {
         if (graph != nullptr) cudaGraphDestroy(graph);
+        cudaGetLastError();  // a failed capture leaves a sticky-looking error behind; it is reported through rc
         return rc;
     }
-    if (e != cudaSuccess || graph == nullptr) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess || graph == nullptr) {
+        cudaGetLastError();
+        return fail("cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    }
     const cudaError_t ei = cudaGraphInstantiate(&plan->exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ei != cudaSuccess) {
         plan->exec = nullptr;
+        cudaGetLastError();
         return fail("cudaGraphInstantiate: %s", cudaGetErrorString(ei));
     }
     plan->captured_ops = plan->ops.size();
@@ -754,21 +767,29 @@ int cpn_ln_im2col2(cpn_plan* plan, const float* x, const float* ln_w, const floa
     auto* lo = static_cast<__nv_bfloat16*>(out_lo);
     set_info("ln_im2col2", 8.0 * ntok * C, 4.0 * ntok * C + 1.0 * B * Ho * Wo * 4 * C * (out_lo != nullptr ? 4 : 2),
              "B=%d H=%d W=%d C=%d s=%d", B, H, W, C, stride);
-    if (lo == nullptr && C % 4 == 0 && C <= 768 && ntok < (1LL << 31) - 65536) {
-        // bf16 mode: vectorised persistent kernel, two tokens in flight per warp
+    if (C % 4 == 0 && C <= 768 && ntok < (1LL << 31) - 65536 && (lo == nullptr || C == 96 || C == 192 || C == 384)) {
+        // vectorised persistent kernels, two tokens in flight per warp
         const int nv = (C / 4 + 31) / 32;
         long long want = (ntok + 15) / 16;
         const long long cap = 8LL * num_sms();
         const int pgrid = static_cast<int>(want < cap ? want : cap);
         static const bool v3 = getenv("CPN_LNIM_V2") == nullptr;
-        if (v3 && (C == 96 || C == 192 || C == 384)) {
+        if ((v3 || lo != nullptr) && (C == 96 || C == 192 || C == 384)) {
             const int tpw = 32 / (C / 12);
             long long want3 = (ntok + 16 * tpw - 1) / (16 * tpw);  // 8 warps x 2 passes x tpw tokens per CTA
             const int pgrid3 = static_cast<int>(want3 < cap ? want3 : cap);
             return submit(plan, stream, [=](cudaStream_t st) -> int {
-                if (C == 96) CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<8>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
-                else if (C == 192) CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<16>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
-                else CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<32>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, B, H, W, stride, Ho, Wo, eps));
+#define CPN_LNIM3(LPT)                                                                                                     \
+    if (lo != nullptr)                                                                                                     \
+        CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<LPT, true>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, lo, B, H, W, \
+                            stride, Ho, Wo, eps));                                                                         \
+    else                                                                                                                   \
+        CPN_CUDA(launch_pdl(cpn::ln_im2col3_bf16_kernel<LPT, false>, pgrid3, dim3(256), 0, st, 1, x, ln_w, ln_b, hi, lo, B, H, W, \
+                            stride, Ho, Wo, eps));
+                if (C == 96) { CPN_LNIM3(8) }
+                else if (C == 192) { CPN_LNIM3(16) }
+                else { CPN_LNIM3(32) }
+#undef CPN_LNIM3
                 CPN_CUDA(cudaGetLastError());
                 return 0;
             });

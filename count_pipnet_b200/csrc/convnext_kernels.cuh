@@ -457,10 +457,12 @@ ln_im2col2_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
 // float4 per lane, so a warp normalises 32 / LPT tokens per pass with log2(LPT) shuffle levels and every lane busy
 // (the generic kernel above leaves 8 of 32 lanes idle at C = 96 and spends most of its time on per-token index math).
 // Two passes are in flight per warp; warps stride over the token list (persistent grid).
-template <int LPT>
+// SPLIT (fp32 mode): the normalised value is written as hi + lo bf16 planes.
+template <int LPT, bool SPLIT = false>
 __global__ void __launch_bounds__(256)
 ln_im2col3_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
-                       __nv_bfloat16* __restrict__ out, int B, int H, int W, int stride, int Ho, int Wo, float eps) {
+                       __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, int B, int H, int W, int stride,
+                       int Ho, int Wo, float eps) {
     constexpr int TPW = 32 / LPT;  // tokens per warp and pass
     constexpr int C = 12 * LPT;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -504,11 +506,17 @@ ln_im2col3_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
             for (int o = LPT / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
             const float rstd = rsqrtf(ss * inv_c + eps);
             if (tok[u] >= ntok) continue;
-            uint2 pk[3];
+            uint2 pk[3], pl[3];
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
-                pk[i].x = pack_bf16x2(fmaf(v[u][i].x * rstd, gw[i].x, gb[i].x), fmaf(v[u][i].y * rstd, gw[i].y, gb[i].y));
-                pk[i].y = pack_bf16x2(fmaf(v[u][i].z * rstd, gw[i].z, gb[i].z), fmaf(v[u][i].w * rstd, gw[i].w, gb[i].w));
+                const float y0 = fmaf(v[u][i].x * rstd, gw[i].x, gb[i].x), y1 = fmaf(v[u][i].y * rstd, gw[i].y, gb[i].y);
+                const float y2 = fmaf(v[u][i].z * rstd, gw[i].z, gb[i].z), y3 = fmaf(v[u][i].w * rstd, gw[i].w, gb[i].w);
+                pk[i].x = pack_bf16x2(y0, y1);
+                pk[i].y = pack_bf16x2(y2, y3);
+                if (SPLIT) {
+                    pl[i].x = pack_bf16x2(y0 - __uint_as_float(pk[i].x << 16), y1 - __uint_as_float(pk[i].x & 0xffff0000u));
+                    pl[i].y = pack_bf16x2(y2 - __uint_as_float(pk[i].y << 16), y3 - __uint_as_float(pk[i].y & 0xffff0000u));
+                }
             }
             const int row = tok[u] / W;
             const int w = tok[u] - row * W;
@@ -526,10 +534,16 @@ ln_im2col3_bf16_kernel(const float* __restrict__ x, const float* __restrict__ ln
                     wo = ww >> 1;
                 }
                 if (ho >= Ho || wo >= Wo) continue;
-                uint2* o = reinterpret_cast<uint2*>(out + ((static_cast<size_t>(b) * Ho + ho) * Wo + wo) * (4 * static_cast<size_t>(C)) +
-                                                    static_cast<size_t>(kk) * C);
+                const size_t off = ((static_cast<size_t>(b) * Ho + ho) * Wo + wo) * (4 * static_cast<size_t>(C)) +
+                                   static_cast<size_t>(kk) * C;
+                uint2* o = reinterpret_cast<uint2*>(out + off);
 #pragma unroll
                 for (int i = 0; i < 3; ++i) o[l + LPT * i] = pk[i];
+                if (SPLIT) {
+                    uint2* ol = reinterpret_cast<uint2*>(out_lo + off);
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) ol[l + LPT * i] = pl[i];
+                }
             }
         }
     }

@@ -178,8 +178,12 @@ def network_forward(model: nn.Module, xs: torch.Tensor, inference: bool = False)
             _fill_gumbel(rec.outs["noise"], model)
             if _e.USE_GRAPHS and rec.runs == 1 and not rec.plan.has_graph:
                 # second forward of this shape: the kernels are loaded and their attributes set, so the launch
-                # sequence can be captured; every later forward is one cudaGraphLaunch
-                rec.plan.capture()
+                # sequence can be captured; every later forward is one cudaGraphLaunch. A plan that cannot be captured
+                # keeps replaying its launch list (same kernels, same results); the reason is kept for inspection.
+                try:
+                    rec.plan.capture()
+                except _lib.CpnError as exc:
+                    model.cpn_graph_error = str(exc)
             rec.plan.run()
             rec.runs += 1
             outs = rec.outs

@@ -345,6 +345,13 @@ def test_ln_im2col2(cuda_device, stride, H, W, C):
     ref = torch.cat(cols, dim=-1).reshape(B * Ho * Wo, 4 * C)
     torch.cuda.synchronize()
     assert (out.float() - ref).abs().max().item() < 0.03
+    # fp32 mode: hi + lo planes
+    hi = torch.zeros_like(out)
+    lo = torch.zeros_like(out)
+    ops.ln_im2col2(x, lw, lb, hi, lo, stride=stride)
+    torch.cuda.synchronize()
+    assert torch.equal(hi, out)
+    assert ((hi.float() + lo.float()) - ref).abs().max().item() < 1e-4
 
 
 @pytest.mark.parametrize("mode", [_lib.POOL_MAX, _lib.POOL_SUM])

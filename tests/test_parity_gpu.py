@@ -151,6 +151,32 @@ def test_prototype_argmax_without_map(cuda_device, name, precision):
         assert (am.cpu().numpy() == g["map_argmax"])[clear].mean() > 0.9
 
 
+def test_plan_is_replayed_as_cuda_graph(cuda_device):
+    """From its second forward on a recorded plan is one CUDA graph launch (small batches are launch-bound otherwise:
+    the reference's visualisation / attribution callers run B = 1, util/vis_pipnet.py:208-213); results are identical."""
+    from count_pipnet_b200 import engine
+    if not engine.USE_GRAPHS:
+        pytest.skip("CPN_GRAPHS=0")
+    case = dict(cases.CASES["count_linear_softmax"], batch=1)
+    model = cases.build(case, my_pipnet, my_count).to(cuda_device)
+    x = cases.inputs(case).to(cuda_device)
+    with torch.no_grad():
+        outs = [model(x, inference=True) for _ in range(4)]
+    torch.cuda.synchronize()
+    rec = next(reversed(engine.state_for(model, cuda_device).plans.values()))
+    assert getattr(model, "cpn_graph_error", None) is None
+    assert rec.plan.has_graph and rec.runs == 4
+    for o in outs[1:]:
+        assert torch.equal(o[1], outs[0][1]) and torch.equal(o[2], outs[0][2]) and torch.equal(o[0], outs[0][0])
+    # a side stream works too: the graph is launched into the caller's current stream
+    s = torch.cuda.Stream(cuda_device)
+    s.wait_stream(torch.cuda.current_stream(cuda_device))
+    with torch.cuda.stream(s), torch.no_grad():
+        o = model(x, inference=True)
+    s.synchronize()
+    assert torch.equal(o[2], outs[0][2])
+
+
 def test_backbone_standalone_nchw(cuda_device):
     """`net._net(x)` on its own returns NCHW features like the reference backbone."""
     case = cases.CASES["count_linear_softmax"]

@@ -23,14 +23,20 @@ def main():
     ap.add_argument("--net", default="convnext_tiny_26")
     ap.add_argument("--passes", type=int, default=5)
     ap.add_argument("--map", action="store_true")
+    ap.add_argument("--config", default="", help="cfg1..cfg5 of count_pipnet_b200/configs.py (overrides --net/--size/--map)")
     args = ap.parse_args()
-    from count_pipnet_b200 import engine, synth
+    from count_pipnet_b200 import configs, engine, synth
     from count_pipnet_b200.pipnet import pipnet as my_pipnet
     dev = torch.device("cuda:0")
-    with contextlib.redirect_stdout(sys.stderr):
-        model, _ = my_pipnet.get_pipnet(200, synth.make_args(net=args.net, num_features=0))
-    synth.load_synth(model, seed=0)
-    model = model.eval().to(dev)
+    if args.config:
+        cfg = configs.CONFIGS[args.config]
+        model = configs.build_model(args.config).to(dev)
+        args.size, args.map, args.net = cfg["size"], cfg["materialize_map"], args.config
+    else:
+        with contextlib.redirect_stdout(sys.stderr):
+            model, _ = my_pipnet.get_pipnet(200, synth.make_args(net=args.net, num_features=0))
+        synth.load_synth(model, seed=0)
+        model = model.eval().to(dev)
     model.cpn_precision = args.precision
     model.materialize_proto_map = args.map
     x = synth.synth_images(args.batch, args.size).to(dev)
@@ -38,7 +44,7 @@ def main():
         for _ in range(3):
             model(x, inference=True)
     torch.cuda.synchronize()
-    rec = next(iter(engine.state_for(model, dev).plans.values()))
+    rec = next(reversed(engine.state_for(model, dev).plans.values()))
     det = rec.plan.details()
     acc = None
     for _ in range(args.passes):
