@@ -83,14 +83,22 @@ int dwconv7_v2(cpn_plan* plan, const float* x, const float* w49, const float* bi
              tok * C * (4 + 2 + (split ? 2 : 0)) + tok * (C / 32) * 8,
              "B=%d H=%d W=%d C=%d v2 nimg=%d ngb=%d ncb=%d warps=%d rows/seg=%d jobs=%d grid=%d", B, H, W, C, p.nimg, p.ngb,
              p.ncb, p.nwc, p.rows_per_seg, p.njobs, grid);
+    // CPN_DW2_UNROLL=1: the seven-fold unrolled row loop (slots renamed instead of moved); A/B only
+    static const bool unrolled = [] { const char* e = getenv("CPN_DW2_UNROLL"); return e != nullptr && atoi(e) != 0; }();
     return submit(plan, stream, [=](cudaStream_t st) -> int {
+#define CPN_DW2_LAUNCH(SP, RL)                                                                                        \
+    do {                                                                                                              \
+        CPN_CUDA(ensure_smem(cpn::dwconv7_v2_kernel<SP, RL>, smem));                                                  \
+        CPN_CUDA(launch_pdl(cpn::dwconv7_v2_kernel<SP, RL>, dim3(grid), dim3(threads), smem, st, 1, tm, p));          \
+    } while (0)
         if (split) {
-            CPN_CUDA(ensure_smem(cpn::dwconv7_v2_kernel<true>, smem));
-            CPN_CUDA(launch_pdl(cpn::dwconv7_v2_kernel<true>, dim3(grid), dim3(threads), smem, st, 1, tm, p));
+            if (unrolled) CPN_DW2_LAUNCH(true, false);
+            else CPN_DW2_LAUNCH(true, true);
         } else {
-            CPN_CUDA(ensure_smem(cpn::dwconv7_v2_kernel<false>, smem));
-            CPN_CUDA(launch_pdl(cpn::dwconv7_v2_kernel<false>, dim3(grid), dim3(threads), smem, st, 1, tm, p));
+            if (unrolled) CPN_DW2_LAUNCH(false, false);
+            else CPN_DW2_LAUNCH(false, true);
         }
+#undef CPN_DW2_LAUNCH
         CPN_CUDA(cudaGetLastError());
         return 0;
     });

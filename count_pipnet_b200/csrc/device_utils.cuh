@@ -1,5 +1,7 @@
 // Small device helpers shared by the kernels: warp reductions, packed fp32x2 arithmetic, bf16 packing.
 #pragma once
+#include <type_traits>
+
 #include "ptx.cuh"
 
 namespace cpn {
@@ -33,5 +35,20 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 }
 __device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 __device__ __forceinline__ uint32_t pack2(float a, float b) { return pack_bf16x2(a, b); }
+
+// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N), so that I can be an asm immediate.
+template <int I, int N>
+struct StaticFor {
+    template <class F>
+    __device__ __forceinline__ static void run(F&& f) {
+        f(std::integral_constant<int, I>{});
+        StaticFor<I + 1, N>::run(f);
+    }
+};
+template <int N>
+struct StaticFor<N, N> {
+    template <class F>
+    __device__ __forceinline__ static void run(F&&) {}
+};
 
 }  // namespace cpn

@@ -39,21 +39,6 @@ constexpr int DWS_TW = 4;      // output columns per lane
 constexpr int DWS_DEPTH = 3;   // rows in flight ahead of the one being consumed
 constexpr int DWS_NSLOT = DWS_DEPTH + 1;
 
-// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N), so that I can be an asm immediate.
-template <int I, int N>
-struct StaticFor {
-    template <class F>
-    __device__ __forceinline__ static void run(F&& f) {
-        f(std::integral_constant<int, I>{});
-        StaticFor<I + 1, N>::run(f);
-    }
-};
-template <int N>
-struct StaticFor<N, N> {
-    template <class F>
-    __device__ __forceinline__ static void run(F&&) {}
-};
-
 __device__ __forceinline__ float2 ldg_f2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
 template <int C, int MAXREG, int TW = DWS_TW>

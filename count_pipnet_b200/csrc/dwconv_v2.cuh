@@ -23,6 +23,8 @@
 //     contiguous range, so the tail of the grid is one short job instead of a partial wave. Row segments cost only
 //     their halo rows' loads: filter rows whose output row lies outside the segment are skipped (uniform branches).
 #pragma once
+#include <type_traits>
+
 #include "device_utils.cuh"
 
 namespace cpn {
@@ -69,7 +71,7 @@ __device__ __forceinline__ Dw2Job dw2_decode(const Dw2Params& p, int job) {
     return j;
 }
 
-template <bool SPLIT>
+template <bool SPLIT, bool ROLL>
 __global__ void __launch_bounds__(32 * (DW2_MAX_WARPS + 1), 2)
 dwconv7_v2_kernel(const __grid_constant__ CUtensorMap tmap_x, const Dw2Params p) {
     constexpr int TW = DW2_TW, NS = DW2_NSTAGE, NIN = TW + 6;
@@ -175,84 +177,103 @@ dwconv7_v2_kernel(const __grid_constant__ CUtensorMap tmap_x, const Dw2Params p)
 
         float2 acc[7][TW];
         const int total_r = jb.nout + 6;  // input rows h0 - 3 .. h0 + nout + 2, in or outside the image
-        for (int rb = 0; rb < total_r; rb += 7) {
+        // One input row. J is the accumulator slot that the row opens (its output row r through filter row 0); filter
+        // row kh accumulates into slot (J - kh) mod 7 and slot (J + 1) mod 7 holds the output row r - 6 this row completes.
+        auto do_row = [&](auto jc, const int r) {
+            constexpr int j = decltype(jc)::value;
+            const int hr = jb.h0 - 3 + r;
 #pragma unroll
-            for (int j = 0; j < 7; ++j) {
-                const int r = rb + j;
-                if (r >= total_r) break;
-                const int hr = jb.h0 - 3 + r;
-                // input row r opens output row r (segment-local) through filter row 0: bias is its first addend
+            for (int t = 0; t < TW; ++t) acc[j][t] = bs;  // bias is the first addend of the output row
+            if (hr >= 0 && hr < p.H) {
+                ptx::mbar_wait(&full_bar[stage], phase);
+                const uint32_t base = ring0 + static_cast<uint32_t>(stage * p.stage_bytes) + laneoff;
+                float2 cur[NIN];
 #pragma unroll
-                for (int t = 0; t < TW; ++t) acc[j][t] = bs;
-                if (hr >= 0 && hr < p.H) {
-                    ptx::mbar_wait(&full_bar[stage], phase);
-                    const uint32_t base = ring0 + static_cast<uint32_t>(stage * p.stage_bytes) + laneoff;
-                    float2 cur[NIN];
+                for (int i = 0; i < NIN; ++i) cur[i] = ptx::lds_f2((base ^ static_cast<uint32_t>((i & 7) << 4)) + i * 128);
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&empty_bar[stage]);  // the row is in registers: free the slot
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+                // filter row kh feeds output row r - kh, which must lie in [0, nout)
+                const int klo = max(0, r - jb.nout + 1), khi = min(6, r);
 #pragma unroll
-                    for (int i = 0; i < NIN; ++i) cur[i] = ptx::lds_f2((base ^ static_cast<uint32_t>((i & 7) << 4)) + i * 128);
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(&empty_bar[stage]);  // the row is in registers: free the slot
-                    if (++stage == NS) { stage = 0; phase ^= 1; }
-                    // filter row kh feeds output row r - kh, which must lie in [0, nout)
-                    const int klo = max(0, r - jb.nout + 1), khi = min(6, r);
+                for (int kh = 0; kh < 7; ++kh) {
+                    if (kh >= klo && kh <= khi) {
+                        const int s = (j - kh + 7) % 7;
+                        const uint32_t wa = wlane + kh * (4 * 256);
+                        const float4 w01 = ptx::lds_f4(wa), w23 = ptx::lds_f4(wa + 256), w45 = ptx::lds_f4(wa + 512);
+                        const float2 w6 = ptx::lds_f2(wa + 768);
+                        const float2 wk[7] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w),
+                                              make_float2(w23.x, w23.y), make_float2(w23.z, w23.w),
+                                              make_float2(w45.x, w45.y), make_float2(w45.z, w45.w), w6};
 #pragma unroll
-                    for (int kh = 0; kh < 7; ++kh) {
-                        if (kh >= klo && kh <= khi) {
-                            const int s = (j - kh + 7) % 7;
-                            const uint32_t wa = wlane + kh * (4 * 256);
-                            const float4 w01 = ptx::lds_f4(wa), w23 = ptx::lds_f4(wa + 256), w45 = ptx::lds_f4(wa + 512);
-                            const float2 w6 = ptx::lds_f2(wa + 768);
-                            const float2 wk[7] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w),
-                                                  make_float2(w23.x, w23.y), make_float2(w23.z, w23.w),
-                                                  make_float2(w45.x, w45.y), make_float2(w45.z, w45.w), w6};
+                        for (int kw = 0; kw < 7; ++kw)
 #pragma unroll
-                            for (int kw = 0; kw < 7; ++kw)
-#pragma unroll
-                                for (int t = 0; t < TW; ++t) acc[s][t] = ffma2(cur[t + kw], wk[kw], acc[s][t]);
-                        }
+                            for (int t = 0; t < TW; ++t) acc[s][t] = ffma2(cur[t + kw], wk[kw], acc[s][t]);
                     }
                 }
-                if (r >= 6) {
-                    // output row r - 6 is complete (slot (j + 1) % 7)
-                    const int s = (j + 1) % 7;
-                    float a[8];
+            }
+            if (r >= 6) {
+                // output row r - 6 is complete
+                const int s = (j + 1) % 7;
+                float a[8];
 #pragma unroll
-                    for (int t = 0; t < TW; ++t) {
-                        const float v0 = acc[s][t].x, v1 = acc[s][t].y;
-                        const uint32_t pk = pack_bf16x2(v0, v1);
-                        if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(out_p + t * p.C) = pk;
-                        float s0 = __uint_as_float(pk << 16), s1 = __uint_as_float(pk & 0xffff0000u);
-                        if (SPLIT) {
-                            const uint32_t pl = pack_bf16x2(v0 - s0, v1 - s1);
-                            if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(lo_p + t * p.C) = pl;
-                            s0 += __uint_as_float(pl << 16);  // what the three-pass GEMM sees: hi + lo
-                            s1 += __uint_as_float(pl & 0xffff0000u);
-                        }
-                        a[2 * t] = s0 + s1;
-                        a[2 * t + 1] = fmaf(s1, s1, s0 * s0);
+                for (int t = 0; t < TW; ++t) {
+                    const float v0 = acc[s][t].x, v1 = acc[s][t].y;
+                    const uint32_t pk = pack_bf16x2(v0, v1);
+                    if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(out_p + t * p.C) = pk;
+                    float s0 = __uint_as_float(pk << 16), s1 = __uint_as_float(pk & 0xffff0000u);
+                    if (SPLIT) {
+                        const uint32_t pl = pack_bf16x2(v0 - s0, v1 - s1);
+                        if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(lo_p + t * p.C) = pl;
+                        s0 += __uint_as_float(pl << 16);  // what the three-pass GEMM sees: hi + lo
+                        s1 += __uint_as_float(pl & 0xffff0000u);
                     }
-                    // transposing butterfly over the unit's 16 lanes (32 channels): afterwards lane hl holds the total of
-                    // value index hl >> 1; fixed order, so results are run-to-run identical
-                    float b4[4], c2[2];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float send = hi8 ? a[i] : a[i + 4];
-                        const float keep = hi8 ? a[i + 4] : a[i];
-                        b4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 2; ++i) {
-                        const float send = hi4 ? b4[i] : b4[i + 2];
-                        const float keep = hi4 ? b4[i + 2] : b4[i];
-                        c2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                    }
-                    float d = (hi2 ? c2[1] : c2[0]) + __shfl_xor_sync(0xffffffffu, hi2 ? c2[0] : c2[1], 2);
-                    d += __shfl_xor_sync(0xffffffffu, d, 1);
-                    if (st_ok) *st_p = d;
-                    out_p += row_elems;
-                    if (SPLIT) lo_p += row_elems;
-                    st_p += st_row;
+                    a[2 * t] = s0 + s1;
+                    a[2 * t + 1] = fmaf(s1, s1, s0 * s0);
                 }
+                // transposing butterfly over the unit's 16 lanes (32 channels): afterwards lane hl holds the total of
+                // value index hl >> 1; fixed order, so results are run-to-run identical
+                float b4[4], c2[2];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float send = hi8 ? a[i] : a[i + 4];
+                    const float keep = hi8 ? a[i + 4] : a[i];
+                    b4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const float send = hi4 ? b4[i] : b4[i + 2];
+                    const float keep = hi4 ? b4[i + 2] : b4[i];
+                    c2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                }
+                float d = (hi2 ? c2[1] : c2[0]) + __shfl_xor_sync(0xffffffffu, hi2 ? c2[0] : c2[1], 2);
+                d += __shfl_xor_sync(0xffffffffu, d, 1);
+                if (st_ok) *st_p = d;
+                out_p += row_elems;
+                if (SPLIT) lo_p += row_elems;
+                st_p += st_row;
+            }
+        };
+        if (ROLL) {
+            // compact loop (fits the instruction cache): every row uses slot 6 for the row it opens and slot 0 for the one
+            // it completes, and the slots move down by one afterwards (48 register moves per row)
+#pragma unroll 1
+            for (int r = 0; r < total_r; ++r) {
+                do_row(std::integral_constant<int, 6>{}, r);
+#pragma unroll
+                for (int sl = 0; sl < 6; ++sl)
+#pragma unroll
+                    for (int t = 0; t < TW; ++t) acc[sl][t] = acc[sl + 1][t];
+            }
+        } else {
+            // slots renamed instead of moved: seven copies of the row body (76 KB of code)
+            for (int rb = 0; rb < total_r; rb += 7) {
+                bool more = true;
+                StaticFor<0, 7>::run([&](auto jc) {
+                    constexpr int j = decltype(jc)::value;
+                    if (more && rb + j < total_r) do_row(jc, rb + j);
+                    else more = false;
+                });
             }
         }
     }

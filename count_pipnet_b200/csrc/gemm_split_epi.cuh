@@ -256,13 +256,12 @@ gemm_split_epi_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
                         uint32_t ph[4], pl[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            float v[2];
-#pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                const int i = 2 * e + h;
-                                const float a = __uint_as_float(r0[8 * j + i]);
-                                v[h] = gelu_erf(fmaf(a, ln_rs, fmaf(ln_nm, ss[i], bb[i])));
-                            }
+                            const int i0 = 2 * e;
+                            const float2 pre = make_float2(
+                                fmaf(__uint_as_float(r0[8 * j + i0]), ln_rs, fmaf(ln_nm, ss[i0], bb[i0])),
+                                fmaf(__uint_as_float(r0[8 * j + i0 + 1]), ln_rs, fmaf(ln_nm, ss[i0 + 1], bb[i0 + 1])));
+                            const float2 ge = gelu_erfc2(pre);
+                            const float v[2] = {ge.x, ge.y};
                             ph[e] = pack_bf16x2(v[0], v[1]);
                             pl[e] = pack_bf16x2(v[0] - __uint_as_float(ph[e] << 16),
                                                 v[1] - __uint_as_float(ph[e] & 0xffff0000u));
