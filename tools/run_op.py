@@ -38,6 +38,16 @@ def main():
         fn = lambda: ops.dwconv7_stats(x, w49, b, out, stats)
         nbytes = x.numel() * 4 + out.numel() * 2 + stats.numel() * 4
         flops = 2.0 * 49 * x.numel()
+    elif a.op == "dwsplit":
+        x = torch.randn(a.B, a.H, a.W, a.C, generator=g).to(dev)
+        w49 = (torch.randn(49, a.C, generator=g) * 0.2).to(dev)
+        b = torch.randn(a.C, generator=g).to(dev)
+        hi = torch.empty(a.B * a.H * a.W, a.C, device=dev, dtype=torch.bfloat16)
+        lo = torch.empty_like(hi)
+        stats = torch.empty(a.B * a.H * a.W, a.C // 32, 2, device=dev)
+        fn = lambda: ops.dwconv7_stats_split(x, w49, b, hi, lo, stats)
+        nbytes = x.numel() * 4 + hi.numel() * 4 + stats.numel() * 4
+        flops = 2.0 * 49 * x.numel()
     elif a.op == "gemm_ln":
         A = torch.randn(a.M, a.K, generator=g).to(dev).to(torch.bfloat16)
         Wt = (torch.randn(a.N, a.K, generator=g) / a.K ** 0.5).to(dev).to(torch.bfloat16)
