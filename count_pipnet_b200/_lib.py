@@ -34,6 +34,7 @@ SIGNATURES = {
     "cpn_ln_im2col2": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
     "cpn_gemm_bf16": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
     "cpn_addon_conv1x1": [_vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _vp],
+    "cpn_addon_softmax_pool": [_vp, _vp, _vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
     "cpn_softmax_pool": [_vp, _vp, _vp, _f, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_softmax_pool_arg": [_vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_pool_argmax_reduce": [_vp, _vp, _vp, _i, _vp, _i, _i, _vp],

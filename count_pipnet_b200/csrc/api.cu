@@ -920,6 +920,34 @@ int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const f
     });
 }
 
+int cpn_addon_softmax_pool(cpn_plan* plan, const float* feat, const float* w, const float* bias, const float* gumbel,
+                           float tau, int hard, int mode, float* map, float* partial, int* partial_arg, int B, int HW, int C,
+                           int P, int chunks, void* stream) {
+    if (P != 16 && P != 32) return fail("cpn_addon_softmax_pool: P must be 16 or 32 (P=%d)", P);
+    if (C <= 0 || C % 64 != 0) return fail("cpn_addon_softmax_pool: C must be a multiple of 64 (C=%d)", C);
+    if (chunks <= 0 || B <= 0 || B > 65535 || HW <= 0) return fail("cpn_addon_softmax_pool: bad chunks / B / HW");
+    if (feat == nullptr || w == nullptr || partial == nullptr) return fail("cpn_addon_softmax_pool: missing operand");
+    const size_t smem = (static_cast<size_t>(C) * P + 8 * 32 * 65 + 2 * 8 * P) * sizeof(float);
+    if (smem > 200 * 1024) return fail("cpn_addon_softmax_pool: C=%d P=%d needs %zu bytes of shared memory", C, P, smem);
+    const dim3 grid(chunks, B);
+    int* parg = (partial_arg != nullptr && mode == CPN_POOL_MAX) ? partial_arg : nullptr;
+    set_info("addon_head", 2.0 * B * HW * C * P, 4.0 * B * HW * (C + P * ((gumbel != nullptr) + (map != nullptr))),
+             "B=%d HW=%d C=%d P=%d chunks=%d", B, HW, C, P, chunks);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        if (P == 16) {
+            CPN_CUDA(ensure_smem(cpn::addon_head_kernel<16>, smem));
+            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<16>, grid, dim3(256), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
+                                map, partial, parg, HW, C, chunks));
+        } else {
+            CPN_CUDA(ensure_smem(cpn::addon_head_kernel<32>, smem));
+            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<32>, grid, dim3(256), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
+                                map, partial, parg, HW, C, chunks));
+        }
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
 int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, float tau, int hard, int mode, float* map,
                          float* partial, int* partial_arg, int B, int HW, int P, int chunks, void* stream) {
     if (chunks <= 0 || B <= 0 || B > 65535) return fail("cpn_softmax_pool: bad chunks/B");

@@ -11,6 +11,8 @@
 
 namespace cpn {
 
+enum PoolMode : int { POOL_MAX = 0, POOL_SUM = 1 };
+
 // ------------------------------------------------------------------------------------------------ add-on conv
 // Warp per patch token, lanes split the C input channels, weights [P][C] staged in shared memory.
 __global__ void __launch_bounds__(256)
@@ -32,8 +34,137 @@ addon_conv1x1_kernel(const float* __restrict__ feat, const float* __restrict__ w
     }
 }
 
+// ------------------------------------------------------------------------------------------------ fused add-on head
+// Add-on 1x1 conv (C -> P, P small) + softmax / hard Gumbel-softmax over P + spatial max or sum, in ONE kernel: the patch
+// logits z [B*HW, P] never exist in HBM (pipnet/pipnet.py:102-108, count_pipnet.py:378-381 + 88). grid = (chunks, B); a warp
+// takes 32 tokens at a time: the feature rows are staged through a padded shared-memory tile in 64-channel slices (coalesced
+// 128-byte loads, conflict-free column reads), then LANE = TOKEN: P dot products in registers with the weights broadcast
+// from shared memory, the softmax in registers, and the per-prototype pooling as a warp reduction over the 32 tokens.
+// gumbel / map are [B, P, HW] (the reference's NCHW layout): coalesced across the tokens of a warp.
+template <int P>
+__global__ void __launch_bounds__(256)
+addon_head_kernel(const float* __restrict__ feat, const float* __restrict__ w, const float* __restrict__ bias,
+                  const float* __restrict__ gumbel, float tau, int hard, int mode, float* __restrict__ map,
+                  float* __restrict__ partial, int* __restrict__ partial_arg, int HW, int C, int chunks) {
+    constexpr int CK = 64, TS = CK + 1, WARPS = 8;
+    extern __shared__ float s_head[];
+    float* s_w = s_head;                          // [C][P]: w transposed, so that a token's P taps of channel c are contiguous
+    float* s_tile = s_w + static_cast<size_t>(C) * P;   // [WARPS][32][TS]
+    float* s_pool = s_tile + WARPS * 32 * TS;     // [WARPS][P]
+    int* s_arg = reinterpret_cast<int*>(s_pool + WARPS * P);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    for (int i = threadIdx.x; i < C * P; i += blockDim.x) {
+        const int pp = i / C, c = i - pp * C;
+        s_w[c * P + pp] = w[i];
+    }
+    __syncthreads();
+    const int per_chunk = (HW + chunks - 1) / chunks;
+    const int t0 = chunk * per_chunk, t1 = min(HW, t0 + per_chunk);
+    const bool want_arg = partial_arg != nullptr && mode == POOL_MAX;
+    float pool[P];
+    int parg[P];
+#pragma unroll
+    for (int pp = 0; pp < P; ++pp) { pool[pp] = 0.f; parg[pp] = 0x7fffffff; }
+    float* tile = s_tile + warp * 32 * TS;
+    for (int tb = t0 + warp * 32; tb < t1; tb += WARPS * 32) {
+        const int t = tb + lane;
+        const bool live = t < t1;
+        float acc[P];
+#pragma unroll
+        for (int pp = 0; pp < P; ++pp) acc[pp] = 0.f;
+        for (int c0 = 0; c0 < C; c0 += CK) {
+            __syncwarp();
+            // stage rows tb .. tb + 31, channels c0 .. c0 + 63: two 128-byte loads per token
+            for (int r = 0; r < 32; ++r) {
+                const int tr = min(tb + r, t1 - 1);
+                const float* f = feat + (static_cast<size_t>(b) * HW + tr) * C + c0;
+                tile[r * TS + lane] = __ldg(f + lane);
+                tile[r * TS + 32 + lane] = __ldg(f + 32 + lane);
+            }
+            __syncwarp();
+            const float* row = tile + lane * TS;
+#pragma unroll 4
+            for (int c = 0; c < CK; ++c) {
+                const float x = row[c];
+                const float4* wv = reinterpret_cast<const float4*>(s_w + static_cast<size_t>(c0 + c) * P);
+#pragma unroll
+                for (int q = 0; q < P / 4; ++q) {
+                    const float4 w4 = wv[q];
+                    acc[4 * q] = fmaf(x, w4.x, acc[4 * q]);
+                    acc[4 * q + 1] = fmaf(x, w4.y, acc[4 * q + 1]);
+                    acc[4 * q + 2] = fmaf(x, w4.z, acc[4 * q + 2]);
+                    acc[4 * q + 3] = fmaf(x, w4.w, acc[4 * q + 3]);
+                }
+            }
+        }
+        // logits (+ Gumbel noise), softmax over the P prototypes of this token
+        const size_t gbase = static_cast<size_t>(b) * P * HW + (live ? t : t1 - 1);
+        float m = -INFINITY;
+        int am = 0;
+#pragma unroll
+        for (int pp = 0; pp < P; ++pp) {
+            float v = acc[pp] + (bias != nullptr ? __ldg(bias + pp) : 0.f);
+            if (gumbel != nullptr) v = (v + __ldg(gumbel + gbase + static_cast<size_t>(pp) * HW)) / tau;
+            acc[pp] = v;
+            if (v > m) { m = v; am = pp; }  // first index on ties, as torch.max
+        }
+        float ssum = 0.f;
+#pragma unroll
+        for (int pp = 0; pp < P; ++pp) {
+            acc[pp] = expf(acc[pp] - m);
+            ssum += acc[pp];
+        }
+        const float inv_s = 1.0f / ssum;
+#pragma unroll
+        for (int pp = 0; pp < P; ++pp) {
+            float y = acc[pp] * inv_s;
+            if (hard) y = ((pp == am ? 1.0f : 0.0f) - y) + y;  // y_hard - y_soft + y_soft (count_pipnet_utils.py:33-38)
+            if (live && map != nullptr) map[gbase + static_cast<size_t>(pp) * HW] = y;
+            if (!live) y = 0.f;  // probabilities are >= 0: neutral for max and sum
+            // pooling over the 32 tokens of the warp (token order; strict comparisons keep the lowest token on ties)
+            if (mode == POOL_MAX) {
+                float bv = y;
+                int bt = live ? t : 0x7fffffff;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                    const int ot = __shfl_xor_sync(0xffffffffu, bt, o);
+                    if (ov > bv || (ov == bv && ot < bt)) { bv = ov; bt = ot; }
+                }
+                if (bv > pool[pp]) { pool[pp] = bv; parg[pp] = bt; }
+            } else {
+                pool[pp] += warp_sum(y);
+            }
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int pp = 0; pp < P; ++pp) {
+            s_pool[warp * P + pp] = pool[pp];
+            s_arg[warp * P + pp] = parg[pp];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < P) {
+        const int pp = threadIdx.x;
+        float a = s_pool[pp];
+        int ai = s_arg[pp];
+        for (int wv = 1; wv < WARPS; ++wv) {
+            const float o = s_pool[wv * P + pp];
+            const int oi = s_arg[wv * P + pp];
+            if (mode == POOL_MAX) {
+                if (o > a || (o == a && oi < ai)) { a = o; ai = oi; }
+            } else {
+                a += o;
+            }
+        }
+        partial[(static_cast<size_t>(b) * chunks + chunk) * P + pp] = a;
+        if (want_arg) partial_arg[(static_cast<size_t>(b) * chunks + chunk) * P + pp] = ai;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ softmax + pool
-enum PoolMode : int { POOL_MAX = 0, POOL_SUM = 1 };
 
 // grid = (chunks, B); each CTA owns a contiguous range of one image's patch tokens, one warp per token at a time.
 // z:       [B, HW, P] fp32 logits (token-major)

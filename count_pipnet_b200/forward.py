@@ -21,6 +21,8 @@ from .programs_resnet import ResNetProgram
 NUM_SMS = 148
 # CTAs of the softmax/pool kernel per SM (each takes a chunk of one image's tokens); env for measurement only
 POOL_CHUNK_FACTOR = float(os.environ.get("CPN_POOL_CHUNKS", "3"))
+# CPN_FUSED_ADDON=0: add-on conv and softmax/pool as two kernels with the logits in HBM (A/B only)
+FUSED_ADDON = os.environ.get("CPN_FUSED_ADDON", "1") != "0"
 
 
 def _make_program(backbone: nn.Module):
@@ -96,11 +98,13 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
     conv, gumbel, tau, is_count, enc, w0, w1, w2 = _head_spec(model)
     plan = em.plan
     T, HW = B * Hf * Wf, Hf * Wf
+    fuse_addon = conv is not None and conv.out_channels in (16, 32) and C % 64 == 0 and FUSED_ADDON
     if conv is not None:
         P = conv.out_channels
-        z = em.buf("z", (T, P), torch.float32)
-        ops.addon_conv1x1(feat, conv.weight.detach().view(P, C), None if conv.bias is None else conv.bias.detach(), z,
-                          T, C, P, plan=plan)
+        if not fuse_addon:
+            z = em.buf("z", (T, P), torch.float32)
+            ops.addon_conv1x1(feat, conv.weight.detach().view(P, C), None if conv.bias is None else conv.bias.detach(), z,
+                              T, C, P, plan=plan)
     else:
         P, z = C, feat
     noise = em.buf("gumbel", (B, P, Hf, Wf), torch.float32) if gumbel else None
@@ -112,8 +116,14 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
     # reference's visualisation search reads off the full map (util/vis_pipnet.py:209-274) without writing the map
     want_arg = bool(getattr(model, "track_prototype_argmax", False)) and not is_count
     parg = em.buf("partial_arg", (B, chunks, P), torch.int32) if want_arg else None
-    ops.softmax_pool(z, partial, B, HW, P, chunks, gumbel=noise, tau=tau, hard=gumbel, mode=mode, map_out=pmap,
-                     partial_arg=parg, plan=plan)
+    if fuse_addon:
+        # add-on conv + softmax + pooling in one kernel: the patch logits never reach HBM
+        ops.addon_softmax_pool(feat, conv.weight.detach().view(P, C), None if conv.bias is None else conv.bias.detach(),
+                               partial, B, HW, C, P, chunks, gumbel=noise, tau=tau, hard=gumbel, mode=mode, map_out=pmap,
+                               partial_arg=parg, plan=plan)
+    else:
+        ops.softmax_pool(z, partial, B, HW, P, chunks, gumbel=noise, tau=tau, hard=gumbel, mode=mode, map_out=pmap,
+                         partial_arg=parg, plan=plan)
     argmax = None
     if want_arg:
         argmax = em.buf("argmax", (B, P), torch.int32)

@@ -157,6 +157,14 @@ def addon_conv1x1(feat, w, b, z, T, Cc, P, plan=None):
     _lib.call("cpn_addon_conv1x1", _ph(plan), ptr(feat), ptr(w), ptr(b), ptr(z), T, Cc, P, _stream())
 
 
+def addon_softmax_pool(feat, w, b, partial, B, HW, Cc, P, chunks, *, gumbel=None, tau=1.0, hard=False,
+                       mode=_lib.POOL_MAX, map_out=None, partial_arg=None, plan=None):
+    """Add-on 1x1 conv + softmax / hard Gumbel + spatial pooling in one kernel (P = 16 or 32): see the header."""
+    _need_cuda(feat, w, b, partial, gumbel, map_out, partial_arg)
+    _lib.call("cpn_addon_softmax_pool", _ph(plan), ptr(feat), ptr(w), ptr(b), ptr(gumbel), float(tau), int(bool(hard)),
+              int(mode), ptr(map_out), ptr(partial), ptr(partial_arg), B, HW, Cc, P, chunks, _stream())
+
+
 def softmax_pool(z, partial, B, HW, P, chunks, *, gumbel=None, tau=1.0, hard=False, mode=_lib.POOL_MAX, map_out=None,
                  partial_arg=None, plan=None):
     """partial_arg [B,chunks,P] int32 (max pooling): token of every chunk maximum, see pool_argmax_reduce."""

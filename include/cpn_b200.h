@@ -132,6 +132,12 @@ int cpn_gemm_bf16(cpn_plan* plan, const void* A, const void* A_lo, const void* B
  * feat [T,C] fp32; w [P,C]; bias [P] or NULL; z [T,P] fp32. */
 int cpn_addon_conv1x1(cpn_plan* plan, const float* feat, const float* w, const float* bias, float* z, long long T,
                       int C, int P, void* stream);
+/* The same add-on conv fused with what follows it (pipnet/pipnet.py:102-108; count_pipnet.py:378-381, 88): 1x1 conv C -> P,
+ * softmax over P (or hard Gumbel-softmax with the given noise), spatial max / sum per chunk of tokens -- one kernel, the
+ * patch logits never reach HBM. Arguments as cpn_addon_conv1x1 + cpn_softmax_pool_arg. P = 16 or 32, C % 64 == 0. */
+int cpn_addon_softmax_pool(cpn_plan* plan, const float* feat, const float* w, const float* bias, const float* gumbel,
+                           float tau, int hard, int mode, float* map, float* partial, int* partial_arg, int B, int HW, int C,
+                           int P, int chunks, void* stream);
 
 /* Per-patch softmax over P (nn.Softmax(dim=1), pipnet/pipnet.py:96,103) or hard Gumbel-softmax with caller-supplied
  * noise (count_pipnet_utils.py:33-38), then spatial max / sum per image as `chunks` partial results.

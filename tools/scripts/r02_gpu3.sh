@@ -2,7 +2,7 @@
 # Round 2, GPU call 3: tensor-core depthwise conv (dwconv_mma.cuh): tests, A/B timings against v1 / v2, step profiles.
 cd /root/repo
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -q -x -k "dwconv7_stats or ln_im2col or ln_gelu_split" > gpurun_out/r02_3_kernels.log 2>&1
+timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -q -x -k "dwconv7_stats or ln_im2col or ln_gelu_split or addon" > gpurun_out/r02_3_kernels.log 2>&1
 echo "kernel tests rc=$?"; tail -12 gpurun_out/r02_3_kernels.log
 for shape in "--B 64 --H 27 --W 27 --C 384" "--B 64 --H 56 --W 56 --C 96" "--B 64 --H 28 --W 28 --C 192" "--B 64 --H 26 --W 26 --C 768" "--B 16 --H 54 --W 54 --C 768" "--B 1 --H 27 --W 27 --C 384"; do
   echo "== $shape"
