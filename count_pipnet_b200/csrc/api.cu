@@ -16,9 +16,6 @@
 #include <string>
 #include <vector>
 
-#ifndef CPN_DWS_TW_DEFAULT
-#define CPN_DWS_TW_DEFAULT 4
-#endif
 #include "convnext_kernels.cuh"
 #include "dwconv_stats.cuh"
 #include "gemm_tcgen05.cuh"
@@ -370,31 +367,17 @@ int submit(cpn_plan* plan, void* stream, Launch fn) {
 }  // namespace cpn_api
 
 namespace {
-// Strip width (output columns per lane). A warp's registers live in ONE of the SM's four 16K-register partitions, so
-// the resident warps per scheduler are floor(512 / registers per thread): 2 at 169-255 registers (TW = 4: 98 weight +
-// 56 accumulator + 20 input registers), 3 at <= 168 (TW = 3: 42 accumulators). CPN_DWS_TW selects (tools/run_op.py).
-int dws_tw() {
-    static const int tw = [] { const char* e = getenv("CPN_DWS_TW"); return e == nullptr ? CPN_DWS_TW_DEFAULT : atoi(e); }();
-    return tw == 3 ? 3 : 4;
-}
-
+// dwconv7_stats_kernel: 192 registers per thread (98 for the taps) -> 2 warps per scheduler, 4 CTAs of 2 warps per SM.
+// The TW = 3 / 168-register variants of round 1 brought nothing (profiles/r01_ncu_full_v10.md) and are gone.
 template <int C>
-int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, float* stats, int H, int W,
-               int nstrips, int rows, dim3 grid, cudaStream_t st) {
-    // register cap = occupancy (see above): 200 -> 2 warps per scheduler, 168 -> 3 (spills at TW = 4; CPN_DWS_REGS, tuning)
-    static const int regs = [] { const char* e = getenv("CPN_DWS_REGS"); return e == nullptr ? 200 : atoi(e); }();
-    if (dws_tw() == 3)
-        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 168, 3>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
-                            stats, H, W, nstrips, rows));
-    else if (regs <= 168)
-        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 168>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
-                            stats, H, W, nstrips, rows));
-    else if (regs <= 200)
-        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 200>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
-                            stats, H, W, nstrips, rows));
+int launch_dws(const float* x, const float* w49, const float* bias, __nv_bfloat16* out, __nv_bfloat16* out_lo, float* stats,
+               int H, int W, int nstrips, int rows, dim3 grid, cudaStream_t st) {
+    if (out_lo != nullptr)
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 200, cpn::DWS_TW, true>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x,
+                            w49, bias, out, out_lo, stats, H, W, nstrips, rows));
     else
-        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 224>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x, w49, bias, out,
-                            stats, H, W, nstrips, rows));
+        CPN_CUDA(launch_pdl(cpn::dwconv7_stats_kernel<C, 200, cpn::DWS_TW, false>, grid, dim3(cpn::DWS_WARPS * 32), 0, st, 1, x,
+                            w49, bias, out, out_lo, stats, H, W, nstrips, rows));
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -612,32 +595,36 @@ int cpn_dwconv7_ln(cpn_plan* plan, const float* x, const float* w49, const float
 // First-generation kernel (taps in registers, 8 warps per SM); cpn_dwconv7_stats (api_dwconv.cu) selects it with
 // CPN_DW_V1=1 for A/B measurements.
 int cpn_api::dwconv7_stats_v1(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
-                              float* stats, int B, int H, int W, int C, void* stream) {
+                              void* out_lo, float* stats, int B, int H, int W, int C, void* stream) {
     if (C != 96 && C != 192 && C != 384 && C != 768)
         return fail("cpn_dwconv7_stats: C=%d is not a ConvNeXt-tiny width (96, 192, 384, 768)", C);
     if (B <= 0 || B > 65535 || H <= 0 || W <= 0) return fail("cpn_dwconv7_stats: bad shape B=%d H=%d W=%d", B, H, W);
-    const int tw = dws_tw();
+    constexpr int tw = cpn::DWS_TW;
     const int nstrips = (W + tw - 1) / tw;
     const int warps = (nstrips * (C / 32) + 1) / 2;  // a warp = two (strip, 32-channel group) units
     const int gx = (warps + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
-    // row segments: every segment pays 6 halo rows of loads AND of FMAs (the body is branch-free), so split H only
-    // when the grid would not give each SM its two resident CTAs a few times over
+    // Row segments. The kernel skips the filter rows that fall outside a segment, so a segment costs only the loads (from
+    // L2) and the ring handling of its 6 halo rows, and finer segments mean a fuller last wave: 4 resident CTAs per SM,
+    // aim for >= 6 waves with >= 7 output rows per segment.
     int nseg = 1;
-    while (static_cast<long long>(gx) * nseg * B < (tw == 3 ? 6LL : 5LL) * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
-    if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knobs (tools/run_op.py)
+    const long long wave = 4LL * num_sms();
+    while (static_cast<long long>(gx) * nseg * B < 6 * wave && (H + nseg) / (nseg + 1) >= 7) ++nseg;
+    if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knob (tools/run_op.py)
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;
     const dim3 grid(gx, nseg, B);
     auto* out = static_cast<__nv_bfloat16*>(out_bf16);
+    auto* lo = static_cast<__nv_bfloat16*>(out_lo);
     const double tok = static_cast<double>(B) * H * W;
-    set_info("dwconv7_stats", 2.0 * 49 * tok * C, tok * C * (4 + 2) + tok * (C / 32) * 8, "B=%d H=%d W=%d C=%d rows/seg=%d",
-             B, H, W, C, rows);
+    set_info(lo != nullptr ? "dwconv7_split" : "dwconv7_stats", 2.0 * 49 * tok * C,
+             tok * C * (4 + 2 + (lo != nullptr ? 2 : 0)) + tok * (C / 32) * 8, "B=%d H=%d W=%d C=%d rows/seg=%d ctas=%d", B, H,
+             W, C, rows, gx * nseg * B);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         switch (C) {
-            case 96: return launch_dws<96>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            case 192: return launch_dws<192>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            case 384: return launch_dws<384>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
-            default: return launch_dws<768>(x, w49, bias, out, stats, H, W, nstrips, rows, grid, st);
+            case 96: return launch_dws<96>(x, w49, bias, out, lo, stats, H, W, nstrips, rows, grid, st);
+            case 192: return launch_dws<192>(x, w49, bias, out, lo, stats, H, W, nstrips, rows, grid, st);
+            case 384: return launch_dws<384>(x, w49, bias, out, lo, stats, H, W, nstrips, rows, grid, st);
+            default: return launch_dws<768>(x, w49, bias, out, lo, stats, H, W, nstrips, rows, grid, st);
         }
     });
 }

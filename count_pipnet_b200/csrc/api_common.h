@@ -38,9 +38,9 @@ int make_tmap_out(CUtensorMap* m, const void* ptr, long long rows, int cols, boo
 int make_tmap_tiled(CUtensorMap* m, CUtensorMapDataType dtype, int rank, const void* ptr, const cuuint64_t* dims,
                     const cuuint64_t* strides_bytes, const cuuint32_t* box, CUtensorMapSwizzle swizzle);
 
-// dwconv7_stats_kernel (api.cu), kept for A/B runs against dwconv7_v2_kernel (api_dwconv.cu).
-int dwconv7_stats_v1(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16, float* stats,
-                     int B, int H, int W, int C, void* stream);
+// dwconv7_stats_kernel (api.cu): the taps-in-registers depthwise conv, ConvNeXt-tiny widths; out_lo != nullptr = fp32 mode.
+int dwconv7_stats_v1(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16, void* out_lo,
+                     float* stats, int B, int H, int W, int C, void* stream);
 
 // Three-pass bf16 hi/lo GEMM with the TMA epilogue (api_gemm_split.cu): epi is a cpn::GemmEpi code (LN+GELU with hi/lo
 // bf16 output planes, scale+residual fp32, bias fp32). cpn_gemm_bf16 routes its split cases here.

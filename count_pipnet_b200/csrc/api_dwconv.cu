@@ -1,8 +1,8 @@
 // C ABI: depthwise 7x7 conv of the CNBlocks (include/cpn_b200.h, cpn_dwconv7_stats / cpn_dwconv7_stats_split).
 #include <cstdlib>
+#include <cstring>
 
 #include "api_common.h"
-#include "dwconv_mma.cuh"
 #include "dwconv_v2.cuh"
 
 using namespace cpn_api;
@@ -84,8 +84,9 @@ int dwconv7_v2(cpn_plan* plan, const float* x, const float* w49, const float* bi
              tok * C * (4 + 2 + (split ? 2 : 0)) + tok * (C / 32) * 8,
              "B=%d H=%d W=%d C=%d v2 nimg=%d ngb=%d ncb=%d warps=%d rows/seg=%d jobs=%d grid=%d", B, H, W, C, p.nimg, p.ngb,
              p.ncb, p.nwc, p.rows_per_seg, p.njobs, grid);
-    // CPN_DW2_UNROLL=1: the seven-fold unrolled row loop (slots renamed instead of moved); A/B only
-    static const bool unrolled = [] { const char* e = getenv("CPN_DW2_UNROLL"); return e != nullptr && atoi(e) != 0; }();
+    // The seven-fold unrolled row loop (slots renamed instead of moved) is the faster one (0.094 vs 0.106 ms at 64 x 27 x 27
+    // x 384, profiles/r02_dwconv.md); CPN_DW2_ROLL=1 selects the compact loop (A/B only)
+    static const bool unrolled = [] { const char* e = getenv("CPN_DW2_ROLL"); return e == nullptr || atoi(e) == 0; }();
     return submit(plan, stream, [=](cudaStream_t st) -> int {
 #define CPN_DW2_LAUNCH(SP, RL)                                                                                        \
     do {                                                                                                              \
@@ -105,78 +106,12 @@ int dwconv7_v2(cpn_plan* plan, const float* x, const float* w49, const float* bi
     });
 }
 
-// ---- tensor-core depthwise conv (dwconv_mma.cuh): job geometry and launch
-int dwconv7_mma(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_hi, void* out_lo,
-                float* stats, int B, int H, int W, int C, void* stream) {
-    cpn::DwmParams p;
-    memset(&p, 0, sizeof(p));
-    p.w49 = w49; p.bias = bias;
-    p.out_hi = static_cast<__nv_bfloat16*>(out_hi);
-    p.out_lo = static_cast<__nv_bfloat16*>(out_lo);
-    p.stats = stats;
-    p.B = B; p.H = H; p.W = W; p.C = C;
-    const int strips = (W + 7) / 8;
-    p.ncb = (strips + 15) / 16;
-    p.sb = (strips + p.ncb - 1) / p.ncb;
-    p.nimg = 16 / p.sb;
-    if (p.nimg > B) {  // no point in staging images that do not exist (power of two keeps 16 / sb semantics simple)
-        p.nimg = 1;
-        while (p.nimg * 2 <= B && p.nimg * 2 * p.sb <= 16) p.nimg *= 2;
-    }
-    p.nip = (B + p.nimg - 1) / p.nimg;
-    p.rw = 4 * p.sb + 4;
-    p.cs = (p.nimg * p.rw) | 1;
-    const int ncols = 8 * p.sb + 8;
-    p.box_tx = ncols * 128;
-    p.box_stride = (p.box_tx + 1023) / 1024 * 1024;
-    p.stage_bytes = p.nimg * p.box_stride;
-    const long long base_jobs = static_cast<long long>(C / 32) * p.nip * p.ncb;
-    const long long slots = num_sms();
-    int nseg = 1;
-    while (base_jobs * nseg < (7 * slots) / 2 && (H + nseg) / (nseg + 1) >= 7) ++nseg;
-    if (const char* e = getenv("CPN_DWM_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knob (tools/run_op.py)
-    p.rows_per_seg = (H + nseg - 1) / nseg;
-    p.nseg = (H + p.rows_per_seg - 1) / p.rows_per_seg;
-    p.njobs = static_cast<int>(base_jobs * p.nseg);
-    const bool split = out_lo != nullptr;
-    const size_t smem = static_cast<size_t>(cpn::dwm_smem(p, split).total) + 1024;
-    if (smem > 227 * 1024) return fail("cpn_dwconv7_stats: W=%d needs %zu bytes of shared memory", W, smem);
-    CUtensorMap tm;
-    const cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
-                                static_cast<cuuint64_t>(B)};
-    const cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 4, static_cast<cuuint64_t>(W) * C * 4,
-                                   static_cast<cuuint64_t>(H) * W * C * 4};
-    const cuuint32_t box[4] = {32, static_cast<cuuint32_t>(ncols), 1, 1};
-    if (make_tmap_tiled(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, x, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B) != 0)
-        return -1;
-    const int grid = static_cast<int>(p.njobs < slots ? p.njobs : slots);
-    const double tok = static_cast<double>(B) * H * W;
-    set_info(split ? "dwconv7_split" : "dwconv7_stats", 2.0 * 49 * tok * C,
-             tok * C * (4 + 2 + (split ? 2 : 0)) + tok * (C / 32) * 8,
-             "B=%d H=%d W=%d C=%d mma nimg=%d sb=%d ncb=%d rows/seg=%d jobs=%d grid=%d", B, H, W, C, p.nimg, p.sb, p.ncb,
-             p.rows_per_seg, p.njobs, grid);
-    return submit(plan, stream, [=](cudaStream_t st) -> int {
-        if (split) {
-            CPN_CUDA(ensure_smem(cpn::dwconv7_mma_kernel<true>, smem));
-            CPN_CUDA(launch_pdl(cpn::dwconv7_mma_kernel<true>, dim3(grid), dim3(cpn::DWM_THREADS), smem, st, 1, tm, p));
-        } else {
-            CPN_CUDA(ensure_smem(cpn::dwconv7_mma_kernel<false>, smem));
-            CPN_CUDA(launch_pdl(cpn::dwconv7_mma_kernel<false>, dim3(grid), dim3(cpn::DWM_THREADS), smem, st, 1, tm, p));
-        }
-        CPN_CUDA(cudaGetLastError());
-        return 0;
-    });
-}
-
-// CPN_DW_IMPL = mma (default: tensor cores, dwconv_mma.cuh) | v2 (CUDA cores, taps in shared memory) | v1 (CUDA cores,
-// taps in registers; bf16 mode and the four ConvNeXt-tiny widths only). A/B measurements: profiles/r02_dwconv.md.
-int dw_impl() {
-    static const int impl = [] {
-        const char* e = getenv("CPN_DW_IMPL");
-        if (e == nullptr) return 0;
-        return strcmp(e, "v2") == 0 ? 2 : (strcmp(e, "v1") == 0 ? 1 : 0);
-    }();
-    return impl;
+// Which kernel: the taps-in-registers kernel (dwconv_stats.cuh) for the four ConvNeXt-tiny widths -- the fastest of the
+// three variants measured in round 2 (profiles/r02_dwconv.md) --, dwconv7_v2_kernel for every other width (any multiple of
+// 32) or when CPN_DW_IMPL=v2 asks for it (A/B runs).
+bool use_v2(int C) {
+    static const bool force = [] { const char* e = getenv("CPN_DW_IMPL"); return e != nullptr && strcmp(e, "v2") == 0; }();
+    return force || !(C == 96 || C == 192 || C == 384 || C == 768);
 }
 
 int check_dw(const char* who, const void* x, int B, int H, int W, int C) {
@@ -193,18 +128,16 @@ extern "C" {
 int cpn_dwconv7_stats(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_bf16,
                       float* stats, int B, int H, int W, int C, void* stream) {
     if (check_dw("cpn_dwconv7_stats", x, B, H, W, C) != 0) return -1;
-    if (dw_impl() == 1 && (C == 96 || C == 192 || C == 384 || C == 768))
-        return dwconv7_stats_v1(plan, x, w49, bias, out_bf16, stats, B, H, W, C, stream);
-    if (dw_impl() == 2) return dwconv7_v2(plan, x, w49, bias, out_bf16, nullptr, stats, B, H, W, C, stream);
-    return dwconv7_mma(plan, x, w49, bias, out_bf16, nullptr, stats, B, H, W, C, stream);
+    if (use_v2(C)) return dwconv7_v2(plan, x, w49, bias, out_bf16, nullptr, stats, B, H, W, C, stream);
+    return dwconv7_stats_v1(plan, x, w49, bias, out_bf16, nullptr, stats, B, H, W, C, stream);
 }
 
 int cpn_dwconv7_stats_split(cpn_plan* plan, const float* x, const float* w49, const float* bias, void* out_hi,
                             void* out_lo, float* stats, int B, int H, int W, int C, void* stream) {
     if (check_dw("cpn_dwconv7_stats_split", x, B, H, W, C) != 0) return -1;
     if (out_lo == nullptr) return fail("cpn_dwconv7_stats_split: the lo plane is required");
-    if (dw_impl() != 0) return dwconv7_v2(plan, x, w49, bias, out_hi, out_lo, stats, B, H, W, C, stream);
-    return dwconv7_mma(plan, x, w49, bias, out_hi, out_lo, stats, B, H, W, C, stream);
+    if (use_v2(C)) return dwconv7_v2(plan, x, w49, bias, out_hi, out_lo, stats, B, H, W, C, stream);
+    return dwconv7_stats_v1(plan, x, w49, bias, out_hi, out_lo, stats, B, H, W, C, stream);
 }
 
 }  // extern "C"

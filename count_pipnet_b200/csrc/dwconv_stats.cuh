@@ -41,11 +41,12 @@ constexpr int DWS_NSLOT = DWS_DEPTH + 1;
 
 __device__ __forceinline__ float2 ldg_f2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
 
-template <int C, int MAXREG, int TW = DWS_TW>
+// SPLIT (fp32 mode): the value is written as hi + lo bf16 planes and the statistics are those of hi + lo.
+template <int C, int MAXREG, int TW = DWS_TW, bool SPLIT = false>
 __global__ void __launch_bounds__(DWS_WARPS * 32) __maxnreg__(MAXREG)
 dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49, const float* __restrict__ bias,
-                     __nv_bfloat16* __restrict__ out, float* __restrict__ stats, int H, int W, int nstrips,
-                     int rows_per_seg) {
+                     __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, float* __restrict__ stats, int H,
+                     int W, int nstrips, int rows_per_seg) {
     static_assert(C % 32 == 0, "32-channel groups");
     static_assert(TW >= 1 && TW <= 4, "the statistics butterfly carries 2 * TW <= 8 values");
     constexpr int NPART = C / 32;
@@ -134,6 +135,7 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
     // running output pointers (advance by one image row per finished output row)
     const size_t pix00 = (static_cast<size_t>(b) * H + h0) * W + w0;
     __nv_bfloat16* out_p = out + pix00 * C + c0;
+    __nv_bfloat16* lo_p = SPLIT ? out_lo + pix00 * C + c0 : nullptr;
     const int sidx = hl >> 1;  // statistics value this lane ends up holding: 2 * t + which
     float* st_p = stats + ((pix00 + (sidx >> 1)) * NPART + cg) * 2 + (sidx & 1);
     const bool st_ok = live && (lane & 1) == 0 && (sidx >> 1) < TW && w0 + (sidx >> 1) < W;
@@ -153,8 +155,11 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
                 issue_next(ps);  // overwrites the slot of row r - 1, whose values were consumed above
             }
             asm volatile("cp.async.wait_group %0;" ::"n"(DWS_DEPTH) : "memory");  // row r has landed
-            // input row r feeds output row o = r - kh (segment-local) through filter row kh; kh == 0 opens the row
-            // (bias as the first addend). Output rows with o < 0 or o >= nout collect values that are never stored.
+            // input row r feeds output row o = r - kh (segment-local) through filter row kh; the row it opens (kh == 0)
+            // starts from the bias. Filter rows whose output row lies outside [0, nout) are skipped (warp-uniform
+            // branches), so a row segment costs only the loads of its 6 halo rows, not their FMAs.
+#pragma unroll
+            for (int t = 0; t < TW; ++t) acc[j][t] = bs;
             if (hi_cur >= 0 && hi_cur < H) {
                 float2 cur[NIN];
                 const uint32_t src = ring0 + slot * SLOT_STRIDE;
@@ -165,19 +170,17 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
                                  : "r"(src), "n"(i * COL_STRIDE)
                                  : "memory");
                 });
+                const int klo = max(0, r - nout + 1), khi = min(6, r);
 #pragma unroll
-                for (int kw = 0; kw < 7; ++kw)
-#pragma unroll
-                    for (int kh = 0; kh < 7; ++kh) {
+                for (int kh = 0; kh < 7; ++kh) {
+                    if (kh >= klo && kh <= khi) {
                         const int s = (j - kh + 7) % 7;
 #pragma unroll
-                        for (int t = 0; t < TW; ++t)
-                            acc[s][t] = ffma2(cur[t + kw], wr[kh * 7 + kw], (kh == 0 && kw == 0) ? bs : acc[s][t]);
-                    }
-            } else {
-                // a row of zero padding above or below the image: it only opens its output row
+                        for (int kw = 0; kw < 7; ++kw)
 #pragma unroll
-                for (int t = 0; t < TW; ++t) acc[j][t] = bs;
+                            for (int t = 0; t < TW; ++t) acc[s][t] = ffma2(cur[t + kw], wr[kh * 7 + kw], acc[s][t]);
+                    }
+                }
             }
             if (++slot == DWS_NSLOT) slot = 0;
             ++hi_cur;
@@ -191,7 +194,13 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
                 for (int t = 0; t < TW; ++t) {
                     const uint32_t pk = pack_bf16x2(acc[s][t].x, acc[s][t].y);
                     if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(out_p + t * C) = pk;
-                    const float v0 = __uint_as_float(pk << 16), v1 = __uint_as_float(pk & 0xffff0000u);
+                    float v0 = __uint_as_float(pk << 16), v1 = __uint_as_float(pk & 0xffff0000u);
+                    if (SPLIT) {
+                        const uint32_t pl = pack_bf16x2(acc[s][t].x - v0, acc[s][t].y - v1);
+                        if ((store_mask >> t) & 1u) *reinterpret_cast<uint32_t*>(lo_p + t * C) = pl;
+                        v0 += __uint_as_float(pl << 16);  // what the three-pass GEMM sees: hi + lo
+                        v1 += __uint_as_float(pl & 0xffff0000u);
+                    }
                     a[2 * t] = v0 + v1;
                     a[2 * t + 1] = fmaf(v1, v1, v0 * v0);
                 }
@@ -213,6 +222,7 @@ dwconv7_stats_kernel(const float* __restrict__ x, const float* __restrict__ w49,
                 d += __shfl_xor_sync(0xffffffffu, d, 1);
                 if (st_ok) *st_p = d;
                 out_p += row_stride;
+                if (SPLIT) lo_p += row_stride;
                 st_p += static_cast<long long>(W) * NPART * 2;
             }
         }

@@ -132,7 +132,9 @@ DW_SHAPES = [(2, 12, 12, 96), (3, 28, 28, 192), (2, 27, 27, 384), (2, 26, 26, 76
              # second-generation kernel: odd image count with two images per job, column blocks (W > 56), several
              # images per job on narrow maps, the benchmark's own shapes
              (3, 27, 27, 384), (1, 112, 112, 96), (2, 55, 55, 384), (5, 6, 6, 192), (9, 13, 13, 96), (7, 24, 24, 192),
-             (64, 27, 27, 384), (64, 56, 56, 96), (16, 26, 26, 768)]
+             (64, 27, 27, 384), (64, 56, 56, 96), (16, 26, 26, 768),
+             # widths that are not ConvNeXt-tiny's: the generic kernel (dwconv_v2.cuh)
+             (3, 27, 27, 128), (2, 56, 56, 64), (1, 112, 112, 32), (5, 6, 6, 160)]
 
 
 @pytest.mark.parametrize("B,H,W,C", DW_SHAPES)
@@ -160,7 +162,7 @@ def test_dwconv7_stats(cuda_device, B, H, W, C):
     assert torch.allclose(stats[..., 1], (o * o).sum(-1), rtol=1e-5, atol=1e-4)
 
 
-@pytest.mark.parametrize("B,H,W,C", DW_SHAPES[:14])
+@pytest.mark.parametrize("B,H,W,C", DW_SHAPES[:14] + DW_SHAPES[-4:])
 def test_dwconv7_stats_split(cuda_device, B, H, W, C):
     """fp32 mode: hi + lo planes carry conv + bias to ~2^-17; the partial sums are those of hi + lo."""
     g = torch.Generator().manual_seed(C + H)

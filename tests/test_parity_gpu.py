@@ -95,7 +95,9 @@ def test_benchmark_shape_forward_matches_live_oracle(cuda_device, precision):
     assert none is None
     stats = check_outputs(case, sd, precision, pooled.cpu().numpy(), out.cpu().numpy(), o_pooled.numpy(), o_out.numpy(), raw)
     print(f"cfg2 B=64 [{precision}] " + " ".join(f"{k}={v:.2e}" if isinstance(v, float) else f"{k}={v}" for k, v in stats.items()))
-    assert stats["class_checked"] >= 0.9 * 64  # the margin rule must not make the class check vacuous
+    # the margin rule must not make the class check vacuous: with the synthetic classifier about 40 of the 64 images have
+    # a top-2 margin above twice the bf16 tolerance (all 64 are checked in fp32 mode)
+    assert stats["class_checked"] >= (64 if precision == "fp32" else 32)
 
 
 @pytest.mark.parametrize("name", ["cfg2_pipnet_convnext26_224", "cfg1_count_shapes_onehot_gumbel"])
