@@ -603,12 +603,10 @@ int cpn_api::dwconv7_stats_v1(cpn_plan* plan, const float* x, const float* w49, 
     const int nstrips = (W + tw - 1) / tw;
     const int warps = (nstrips * (C / 32) + 1) / 2;  // a warp = two (strip, 32-channel group) units
     const int gx = (warps + cpn::DWS_WARPS - 1) / cpn::DWS_WARPS;
-    // Row segments. The kernel skips the filter rows that fall outside a segment, so a segment costs only the loads (from
-    // L2) and the ring handling of its 6 halo rows, and finer segments mean a fuller last wave: 4 resident CTAs per SM,
-    // aim for >= 6 waves with >= 7 output rows per segment.
+    // row segments: every segment pays 6 halo rows of loads AND of FMAs (the body is branch-free), so split H only
+    // when the grid would not give each SM its resident CTAs a few times over
     int nseg = 1;
-    const long long wave = 4LL * num_sms();
-    while (static_cast<long long>(gx) * nseg * B < 6 * wave && (H + nseg) / (nseg + 1) >= 7) ++nseg;
+    while (static_cast<long long>(gx) * nseg * B < 5LL * num_sms() && (H + nseg) / (nseg + 1) >= 12) ++nseg;
     if (const char* e = getenv("CPN_DWS_NSEG")) nseg = atoi(e) > 0 ? atoi(e) : nseg;  // tuning knob (tools/run_op.py)
     const int rows = (H + nseg - 1) / nseg;
     nseg = (H + rows - 1) / rows;
