@@ -912,7 +912,7 @@ int cpn_addon_softmax_pool(cpn_plan* plan, const float* feat, const float* w, co
     if (C <= 0 || C % 64 != 0) return fail("cpn_addon_softmax_pool: C must be a multiple of 64 (C=%d)", C);
     if (chunks <= 0 || B <= 0 || B > 65535 || HW <= 0) return fail("cpn_addon_softmax_pool: bad chunks / B / HW");
     if (feat == nullptr || w == nullptr || partial == nullptr) return fail("cpn_addon_softmax_pool: missing operand");
-    const size_t smem = (static_cast<size_t>(C) * P + 8 * 32 * 65 + 2 * 8 * P) * sizeof(float);
+    const size_t smem = (static_cast<size_t>(C) * P + cpn::ADDON_WARPS * (32 * 65 + 2 * P)) * sizeof(float);
     if (smem > 200 * 1024) return fail("cpn_addon_softmax_pool: C=%d P=%d needs %zu bytes of shared memory", C, P, smem);
     const dim3 grid(chunks, B);
     int* parg = (partial_arg != nullptr && mode == CPN_POOL_MAX) ? partial_arg : nullptr;
@@ -921,11 +921,11 @@ int cpn_addon_softmax_pool(cpn_plan* plan, const float* feat, const float* w, co
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         if (P == 16) {
             CPN_CUDA(ensure_smem(cpn::addon_head_kernel<16>, smem));
-            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<16>, grid, dim3(256), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
+            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<16>, grid, dim3(32 * cpn::ADDON_WARPS), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
                                 map, partial, parg, HW, C, chunks));
         } else {
             CPN_CUDA(ensure_smem(cpn::addon_head_kernel<32>, smem));
-            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<32>, grid, dim3(256), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
+            CPN_CUDA(launch_pdl(cpn::addon_head_kernel<32>, grid, dim3(32 * cpn::ADDON_WARPS), smem, st, 1, feat, w, bias, gumbel, tau, hard, mode,
                                 map, partial, parg, HW, C, chunks));
         }
         CPN_CUDA(cudaGetLastError());

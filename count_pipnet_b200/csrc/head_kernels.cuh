@@ -41,12 +41,13 @@ addon_conv1x1_kernel(const float* __restrict__ feat, const float* __restrict__ w
 // 128-byte loads, conflict-free column reads), then LANE = TOKEN: P dot products in registers with the weights broadcast
 // from shared memory, the softmax in registers, and the per-prototype pooling as a warp reduction over the 32 tokens.
 // gumbel / map are [B, P, HW] (the reference's NCHW layout): coalesced across the tokens of a warp.
+constexpr int ADDON_WARPS = 4;
 template <int P>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(32 * ADDON_WARPS)
 addon_head_kernel(const float* __restrict__ feat, const float* __restrict__ w, const float* __restrict__ bias,
                   const float* __restrict__ gumbel, float tau, int hard, int mode, float* __restrict__ map,
                   float* __restrict__ partial, int* __restrict__ partial_arg, int HW, int C, int chunks) {
-    constexpr int CK = 64, TS = CK + 1, WARPS = 8;
+    constexpr int CK = 64, TS = CK + 1, WARPS = ADDON_WARPS;
     extern __shared__ float s_head[];
     float* s_w = s_head;                          // [C][P]: w transposed, so that a token's P taps of channel c are contiguous
     float* s_tile = s_w + static_cast<size_t>(C) * P;   // [WARPS][32][TS]
@@ -75,12 +76,22 @@ addon_head_kernel(const float* __restrict__ feat, const float* __restrict__ w, c
         for (int pp = 0; pp < P; ++pp) acc[pp] = 0.f;
         for (int c0 = 0; c0 < C; c0 += CK) {
             __syncwarp();
-            // stage rows tb .. tb + 31, channels c0 .. c0 + 63: two 128-byte loads per token
-            for (int r = 0; r < 32; ++r) {
-                const int tr = min(tb + r, t1 - 1);
-                const float* f = feat + (static_cast<size_t>(b) * HW + tr) * C + c0;
-                tile[r * TS + lane] = __ldg(f + lane);
-                tile[r * TS + 32 + lane] = __ldg(f + 32 + lane);
+            // stage rows tb .. tb + 31, channels c0 .. c0 + 63: two 128-byte loads per token, 16 loads in flight
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 8) {
+                float v[8][2];
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) {
+                    const int tr = min(tb + r0 + rr, t1 - 1);
+                    const float* f = feat + (static_cast<size_t>(b) * HW + tr) * C + c0;
+                    v[rr][0] = __ldg(f + lane);
+                    v[rr][1] = __ldg(f + 32 + lane);
+                }
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) {
+                    tile[(r0 + rr) * TS + lane] = v[rr][0];
+                    tile[(r0 + rr) * TS + 32 + lane] = v[rr][1];
+                }
             }
             __syncwarp();
             const float* row = tile + lane * TS;

@@ -109,6 +109,9 @@ def _emit_head(em: Emit, model: nn.Module, feat: torch.Tensor, B: int, Hf: int, 
         P, z = C, feat
     noise = em.buf("gumbel", (B, P, Hf, Wf), torch.float32) if gumbel else None
     chunks = max(1, min(max(HW // 8, 1), math.ceil(POOL_CHUNK_FACTOR * NUM_SMS / B)))
+    if fuse_addon:
+        # the fused kernel's CTA = 4 warps x 32 tokens: one 128-token chunk per CTA unless the batch is small
+        chunks = max(chunks, math.ceil(HW / 128))
     partial = em.buf("partial", (B, chunks, P), torch.float32)
     pmap = em.buf("map", (B, P, Hf, Wf), torch.float32) if want_map else None
     mode = _lib.POOL_SUM if is_count else _lib.POOL_MAX
