@@ -43,6 +43,7 @@ SIGNATURES = {
     "cpn_head_tail": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_nhwc_to_nchw": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_nchw_to_nhwc": [_vp, _vp, _vp, _i, _i, _i, _vp],
+    "cpn_conv_bn_act": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_im2col_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_im2col_nchw_f32": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_maxpool3s2": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
@@ -58,6 +59,7 @@ ENC_NONE, ENC_ONEHOT, ENC_LINEAR, ENC_LINEAR_FULL, ENC_BILINEAR, ENC_IDENTITY = 
 OTHER_SIGNATURES = {
     "cpn_last_error": ([], C.c_char_p),
     "cpn_plan_op_detail": ([_vp, _i], C.c_char_p),
+    "cpn_conv3x3_tile_rows": ([_i, _i], C.c_int),  # a count, not a status
 }
 
 

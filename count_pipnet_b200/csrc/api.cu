@@ -941,7 +941,7 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
     if (smem > 200 * 1024) return fail("cpn_softmax_pool: P=%d too large", P);
     const dim3 grid(chunks, B);
     set_info("softmax_pool", 4.0 * B * HW * P, 4.0 * B * HW * P * (1 + (gumbel != nullptr) + (map != nullptr)));
-    if (gumbel == nullptr && !hard && map == nullptr && P % 128 == 0 && P <= 1024) {
+    if (gumbel == nullptr && !hard && map == nullptr && P % 128 == 0 && (P <= 1024 || P == 2048)) {
         // plain softmax, map not requested: register-resident kernel
         const int nv = P / 128;
         return submit(plan, stream, [=](cudaStream_t st) -> int {
@@ -959,6 +959,17 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
             switch (nv) {
                 CPN_SMP_CASE(1) CPN_SMP_CASE(2) CPN_SMP_CASE(3) CPN_SMP_CASE(4)
                 CPN_SMP_CASE(5) CPN_SMP_CASE(6) CPN_SMP_CASE(7) CPN_SMP_CASE(8)
+                case 16:  // P = 2048 (ResNet-50): one token in flight per warp
+                    if (arg) {
+                        CPN_CUDA(ensure_smem(cpn::softmax_pool_reg_kernel<16, true, 1>, smem));
+                        CPN_CUDA(launch_pdl(cpn::softmax_pool_reg_kernel<16, true, 1>, grid, dim3(256), smem, st, 1, z, mode,
+                                            partial, partial_arg, HW, chunks));
+                    } else {
+                        CPN_CUDA(ensure_smem(cpn::softmax_pool_reg_kernel<16, false, 1>, smem));
+                        CPN_CUDA(launch_pdl(cpn::softmax_pool_reg_kernel<16, false, 1>, grid, dim3(256), smem, st, 1, z, mode,
+                                            partial, static_cast<int*>(nullptr), HW, chunks));
+                    }
+                    break;
             }
 #undef CPN_SMP_CASE
             CPN_CUDA(cudaGetLastError());

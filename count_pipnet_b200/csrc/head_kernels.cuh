@@ -316,7 +316,8 @@ __global__ void topk_update_kernel(const float* __restrict__ pooled, const int* 
 // instruction), so the row max / sum are two warp reductions, the probabilities never leave registers and the running
 // spatial max / sum stays in registers too; two tokens are in flight per warp. Same grid and partial layout as above.
 // exp() is ex2.approx of a pre-scaled argument: relative error 2^-22, well inside the fp32-mode parity bar (1e-4).
-template <int NV, bool ARG>
+// U = tokens in flight per warp (2; 1 for P > 1024, where a token alone is 16 independent 512-byte loads and 64 registers).
+template <int NV, bool ARG, int U = 2>
 __global__ void __launch_bounds__(256)
 softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict__ partial,
                         int* __restrict__ partial_arg, int HW, int chunks) {
@@ -339,17 +340,17 @@ softmax_pool_reg_kernel(const float* __restrict__ z, int mode, float* __restrict
 #pragma unroll
     for (int i = 0; i < (ARG ? NV : 1); ++i) parg[i] = make_int4(0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff);
     const float4* zb = reinterpret_cast<const float4*>(z + static_cast<size_t>(b) * HW * P) + lane;
-    for (int t = t0 + 2 * warp; t < t1; t += 2 * wpb) {
+    for (int t = t0 + U * warp; t < t1; t += U * wpb) {
         const bool two = t + 1 < t1;
-        float4 v[2][NV];
+        float4 v[U][NV];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < U; ++u) {
             const float4* zr = zb + static_cast<size_t>(u == 1 && two ? t + 1 : t) * (P / 4);
 #pragma unroll
             for (int i = 0; i < NV; ++i) v[u][i] = __ldg(zr + 32 * i);
         }
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < U; ++u) {
             float m = -INFINITY;
 #pragma unroll
             for (int i = 0; i < NV; ++i) m = fmaxf(fmaxf(fmaxf(v[u][i].x, v[u][i].y), fmaxf(v[u][i].z, v[u][i].w)), m);

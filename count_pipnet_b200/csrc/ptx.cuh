@@ -228,6 +228,14 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & PEER_BIT_MASK), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_4d_2sm(void* smem_dst, const CUtensorMap* m, int c0, int c1, int c2, int c3,
+                                                uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & PEER_BIT_MASK), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 // Arrive on the mbarrier at the same offset in the leader CTA (rank 0 of the pair); usable from either CTA.
 // Default semantics (release at CTA scope): the cluster-scope form costs a MEMBAR.ALL.GPU + ERRBAR per arrive, and
 // what the waiter consumes here (TMEM reads ordered by tcgen05.wait::ld, shared-memory writes already published to

@@ -198,6 +198,19 @@ def nchw_to_nhwc(x, out, B, HW, Cc, plan=None):
     _lib.call("cpn_nchw_to_nhwc", _ph(plan), ptr(x), ptr(out), B, HW, Cc, _stream())
 
 
+def conv3x3_tile_rows(H: int, W: int) -> int:
+    """Image rows per M tile of the implicit 3x3 conv, 0 if this map size needs the im2col path."""
+    return int(_lib.load().cpn_conv3x3_tile_rows(int(H), int(W)))
+
+
+def conv_bn_act(x_bf16, w_bf16, bias, B, H, W, Cin, Cout, ksize, *, relu, res_f32=None, out_f32=None, out_bf16=None,
+                plan=None):
+    """ResNet conv + folded BN (+ReLU / + identity) as one GEMM without im2col: see cpn_conv_bn_act in the header."""
+    _need_cuda(x_bf16, w_bf16, bias, res_f32, out_f32, out_bf16)
+    _lib.call("cpn_conv_bn_act", _ph(plan), ptr(x_bf16), ptr(w_bf16), ptr(bias), ptr(res_f32), ptr(out_f32),
+              ptr(out_bf16), B, H, W, Cin, Cout, int(ksize), int(bool(relu)), _stream())
+
+
 def im2col_bf16(x, out, B, H, W, Cc, k, stride, pad, Kpad, plan=None):
     _need_cuda(x, out)
     _lib.call("cpn_im2col_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, k, stride, pad, Kpad, _stream())

@@ -5,6 +5,7 @@ Layout: channels-last; the block-to-block residual stream is fp32 with a bf16 co
 """
 from __future__ import annotations
 
+import os
 from typing import List, Tuple
 
 import torch
@@ -13,6 +14,10 @@ import torch.nn as nn
 from . import _lib, ops
 from .features import resnet_features as rsn
 from .programs import Emit, _split
+
+
+# CPN_CONV_GEMM=0: every conv through im2col + cpn_gemm_bf16 as in round 1 (A/B only)
+USE_CONV_GEMM = os.environ.get("CPN_CONV_GEMM", "1") != "0"
 
 
 def _fold(conv: nn.Conv2d, bn: nn.BatchNorm2d, split: bool, k_order: str, kpad: int = 0):
@@ -63,6 +68,25 @@ class ResNetProgram:
         Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
         M = B * Ho * Wo
         w_hi, w_lo, bias = folded
+        # bf16 mode: conv + BN (+ReLU / +identity) as one GEMM with a TMA epilogue; 3x3 taps read straight from the
+        # activation (csrc/conv_gemm.cuh). Strided convs gather first (1x1: subsample) or keep the im2col path (3x3).
+        direct = (not em.split and USE_CONV_GEMM and Cout % 64 == 0 and Cin % 64 == 0 and
+                  ((k == 1) or (k == 3 and s == 1 and p == 1 and ops.conv3x3_tile_rows(H, W) > 0)) and
+                  ((relu and res_f32 is None and out_f32 is None and want_bf16) or
+                   (relu and res_f32 is not None and out_f32 is not None and want_bf16) or
+                   (not relu and res_f32 is None and out_f32 is not None and not want_bf16)))
+        if direct:
+            xin = x_hi
+            if k == 1 and s == 2:
+                xin = em.buf("sub_hi", (M, Cin), torch.bfloat16)
+                ops.subsample2_bf16(x_hi, xin, B, H, W, Cin, plan=em.plan)
+            elif k == 1 and s != 1:
+                direct = False
+        if direct:
+            o_hi = em.buf(tag + "_hi", (M, Cout), torch.bfloat16) if want_bf16 else None
+            ops.conv_bn_act(xin, w_hi, bias, B, Ho, Wo, Cin, Cout, k, relu=relu, res_f32=res_f32, out_f32=out_f32,
+                            out_bf16=o_hi, plan=em.plan)
+            return o_hi, None, Ho, Wo
         if k == 1 and s == 1:
             a_hi, a_lo, K = x_hi, x_lo, Cin
         elif k == 1 and s == 2:

@@ -195,6 +195,21 @@ int cpn_nhwc_to_nchw(cpn_plan* plan, const float* x, float* out, int B, int HW, 
 /* [B,C,H,W] fp32 -> [B,H,W,C] fp32 (entry of net._add_on(features) when called on its own). */
 int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, int C, void* stream);
 
+/* ResNet conv + folded BatchNorm (+ ReLU / + identity) as ONE tcgen05 GEMM without an im2col matrix
+ * (features/resnet_features.py:97-117 Bottleneck.forward, :55-74 BasicBlock.forward; eval-mode BN is an affine map).
+ * x_bf16 [B,H,W,Cin] channels-last bf16; w_bf16 [Cout, k*k*Cin] bf16 with K ordered (kh, kw, cin) and the BN scale folded
+ * in; bias [Cout] = the folded BN shift. ksize = 1 (plain GEMM) or 3 (stride 1, pad 1: the nine taps are read from the
+ * activation with 4-D TMA boxes, out-of-map rows / columns arrive as zeros = the padding). Output combinations:
+ *   out_bf16 only, relu = 1                       out_bf16 = relu(conv + bias)                  conv1, conv2
+ *   res_f32 + out_f32 + out_bf16, relu = 1        out_f32 = relu(res_f32 + conv + bias), out_bf16 = bf16(out_f32)   block end
+ *   out_f32 only, relu = 0                        out_f32 = conv + bias                         projection shortcut
+ * Cout % 64 == 0; ksize 3 needs Cin % 64 == 0 and cpn_conv3x3_tile_rows(H, W) > 0 (image rows per 128-row M tile; 0 =
+ * this map size needs the im2col path: cpn_im2col_bf16 + cpn_gemm_bf16). */
+int cpn_conv3x3_tile_rows(int H, int W);
+int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const float* res_f32,
+                    float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
+                    void* stream);
+
 /* im2col rows of a kxk convolution (pad, stride) over a channels-last bf16 map, K padded to Kpad with zeros:
  * out[(b,ho,wo), (kh*k+kw)*C + c] -- feeds cpn_gemm_bf16 for features/resnet_features.py convs. */
 int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, int k, int stride,

@@ -375,7 +375,7 @@ def test_softmax_pool_and_map(cuda_device, mode, P):
 
 
 @pytest.mark.parametrize("mode", [_lib.POOL_MAX, _lib.POOL_SUM])
-@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5)])
+@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5), (2048, 50, 3)])
 def test_softmax_pool_register_path(cuda_device, mode, P, HW, chunks):
     """Plain softmax without the map (register-resident kernel), odd token counts and ragged chunks."""
     g = torch.Generator().manual_seed(P + HW)
@@ -392,7 +392,7 @@ def test_softmax_pool_register_path(cuda_device, mode, P, HW, chunks):
 
 
 @pytest.mark.parametrize("with_map", [False, True])
-@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5), (16, 49, 2)])
+@pytest.mark.parametrize("P,HW,chunks", [(768, 101, 4), (128, 37, 3), (1024, 64, 5), (768, 676, 5), (16, 49, 2), (2048, 50, 3)])
 def test_softmax_pool_argmax(cuda_device, with_map, P, HW, chunks):
     """Token of each prototype's spatial maximum (both softmax kernels), bit-exact incl. ties -> lowest token."""
     g = torch.Generator().manual_seed(P + HW + 1)
@@ -493,6 +493,48 @@ def test_addon_head_fused(cuda_device, mode, B, HW, C, P, chunks, gum):
         tok = parg.gather(1, best)[:, 0, :].long()
         picked = pmap.gather(2, tok[:, :, None])[:, :, 0]
         assert (picked - pmap.amax(2)).abs().max().item() <= 1e-6
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,k,kind", [
+    (2, 28, 28, 128, 128, 3, "relu"), (3, 56, 56, 64, 64, 3, "relu"), (2, 28, 28, 512, 512, 3, "relu"),
+    (32, 28, 28, 256, 256, 3, "relu"), (2, 28, 28, 256, 1024, 1, "res"), (32, 28, 28, 512, 2048, 1, "res"),
+    (2, 56, 56, 64, 256, 1, "bias"), (5, 28, 28, 1024, 512, 1, "relu"), (3, 56, 56, 64, 256, 1, "res"),
+    (1, 28, 28, 64, 64, 3, "res"), (7, 8, 16, 64, 128, 3, "bias")])
+def test_conv_bn_act(cuda_device, B, H, W, Cin, Cout, k, kind):
+    """ResNet conv + folded BN as one GEMM (implicit 3x3 taps, TMA epilogue) vs F.conv2d on the same bf16 operands."""
+    g = torch.Generator().manual_seed(Cin + Cout + k)
+    x = torch.randn(B, H, W, Cin, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(Cout, Cin, k, k, generator=g) / (Cin * k * k) ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(Cout, generator=g).to(cuda_device)
+    wk = w.permute(0, 2, 3, 1).reshape(Cout, k * k * Cin).contiguous()  # K ordered (kh, kw, cin)
+    M = B * H * W
+    if k == 3:
+        assert ops.conv3x3_tile_rows(H, W) > 0
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=k // 2).permute(0, 2, 3, 1).reshape(M, Cout)
+    out32 = torch.full((M, Cout), float("nan"), device=cuda_device)
+    out16 = torch.full((M, Cout), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    if kind == "relu":
+        ops.conv_bn_act(x, wk, bias, B, H, W, Cin, Cout, k, relu=True, out_bf16=out16)
+        ref = torch.relu(ref)
+    elif kind == "res":
+        res = torch.randn(M, Cout, generator=g).to(cuda_device)
+        ops.conv_bn_act(x, wk, bias, B, H, W, Cin, Cout, k, relu=True, res_f32=res, out_f32=out32, out_bf16=out16)
+        ref = torch.relu(ref + res)
+    else:
+        ops.conv_bn_act(x, wk, bias, B, H, W, Cin, Cout, k, relu=False, out_f32=out32)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    if kind != "relu":
+        assert (out32 - ref).abs().max().item() <= 2e-3 * scale  # fp32 accumulation order only
+    if kind != "bias":
+        assert (out16.float() - ref).abs().max().item() <= 2.0 ** -8 * scale + 2e-3 * scale
+    if kind == "res":
+        assert torch.equal(out16, out32.to(torch.bfloat16))
+
+
+def test_conv3x3_tile_rows():
+    assert ops.conv3x3_tile_rows(28, 28) == 4 and ops.conv3x3_tile_rows(56, 56) == 2
+    assert ops.conv3x3_tile_rows(14, 14) == 0 and ops.conv3x3_tile_rows(8, 16) == 8
 
 
 def test_transposes(cuda_device):
