@@ -976,6 +976,26 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
             return 0;
         });
     }
+    if (gumbel == nullptr && !hard && map != nullptr && !arg && P % 128 == 0 && P <= 1024) {
+        // plain softmax with the map written: staged through shared memory so that the map rows go out coalesced
+        const int nv = P / 128;
+        const size_t msmem = (32 + 8) * static_cast<size_t>(P) * sizeof(float);
+        return submit(plan, stream, [=](cudaStream_t st) -> int {
+#define CPN_SMM_CASE(NVV)                                                                                            \
+    case NVV:                                                                                                        \
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_map_kernel<NVV>, msmem));                                             \
+        CPN_CUDA(launch_pdl(cpn::softmax_pool_map_kernel<NVV>, grid, dim3(256), msmem, st, 1, z, mode, map, partial, HW,  \
+                            chunks));                                                                               \
+        break;
+            switch (nv) {
+                CPN_SMM_CASE(1) CPN_SMM_CASE(2) CPN_SMM_CASE(3) CPN_SMM_CASE(4)
+                CPN_SMM_CASE(5) CPN_SMM_CASE(6) CPN_SMM_CASE(7) CPN_SMM_CASE(8)
+            }
+#undef CPN_SMM_CASE
+            CPN_CUDA(cudaGetLastError());
+            return 0;
+        });
+    }
     int* parg = arg ? partial_arg : nullptr;
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         CPN_CUDA(ensure_smem(cpn::softmax_pool_kernel, smem));
@@ -1127,12 +1147,15 @@ int cpn_im2col_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int 
 
 int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, void* out_lo, int B, int C, int H, int W, int k,
                         int stride, int pad, int Kpad, void* stream) {
-    if (Kpad < k * k * C) return fail("cpn_im2col_nchw_f32: Kpad too small");
+    if (Kpad < k * k * C || Kpad % 8 != 0) return fail("cpn_im2col_nchw_f32: Kpad must be a multiple of 8 and >= k*k*C");
+    if ((reinterpret_cast<uintptr_t>(out) & 15) != 0 || (reinterpret_cast<uintptr_t>(out_lo) & 15) != 0)
+        return fail("cpn_im2col_nchw_f32: outputs must be 16-byte aligned");
     const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * Kpad);
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (Kpad / 8));
+    const size_t tab_bytes = 2 * static_cast<size_t>(Kpad) * sizeof(int);
     set_info("im2col_nchw_f32", 0.0, 4.0 * B * C * H * W + 2.0 * B * Ho * Wo * Kpad * (out_lo != nullptr ? 2 : 1));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
-        cpn::im2col_nchw_f32_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(out),
+        cpn::im2col_nchw_f32_kernel<<<grid, 256, tab_bytes, st>>>(x, static_cast<__nv_bfloat16*>(out),
                                                           static_cast<__nv_bfloat16*>(out_lo), B, C, H, W, k, stride,
                                                           pad, Ho, Wo, Kpad);
         CPN_CUDA(cudaGetLastError());

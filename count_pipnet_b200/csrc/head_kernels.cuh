@@ -311,6 +311,101 @@ __global__ void topk_update_kernel(const float* __restrict__ pooled, const int* 
     cnt[p] = n;
 }
 
+// Plain softmax WITH the patch x prototype map written (cfg5: the caller asks for the map for visualisation). The map is
+// [B, P, HW] (the reference's NCHW proto_features), i.e. prototype-major, while a token's probabilities are produced
+// token-major: writing them straight out is one 4-byte store per 128-byte line (the generic kernel: 0.46 ms at cfg5).
+// Here the CTA stages 32 tokens x P probabilities in shared memory (float4 slots XOR-swizzled by token & 7, conflict-free
+// both ways) and writes every prototype's 32 tokens as one 128-byte segment. Pooling as in the register kernel.
+template <int NV>
+__global__ void __launch_bounds__(256)
+softmax_pool_map_kernel(const float* __restrict__ z, int mode, float* __restrict__ map, float* __restrict__ partial, int HW,
+                        int chunks) {
+    constexpr int P = NV * 128, F = P / 4, WARPS = 8, TT = 32;
+    extern __shared__ float s_map[];         // [TT][P] swizzled tile, then [WARPS][P] pooling partials
+    float4* tile = reinterpret_cast<float4*>(s_map);
+    float* s_pool = s_map + TT * P;
+    ptx::pdl_wait();
+    ptx::pdl_launch_dependents();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    const int per_chunk = (HW + chunks - 1) / chunks;
+    const int t0 = chunk * per_chunk, t1 = min(HW, t0 + per_chunk);
+    constexpr float LOG2E = 1.4426950408889634f;
+    float4 pool[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) pool[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* zb = reinterpret_cast<const float4*>(z + static_cast<size_t>(b) * HW * P) + lane;
+    float* mb = map + static_cast<size_t>(b) * P * HW;
+    for (int tb = t0; tb < t1; tb += TT) {
+        // ---- each warp: 4 tokens of the tile, probabilities to the pool and to the shared tile
+#pragma unroll 1
+        for (int u = 0; u < TT / WARPS; ++u) {
+            const int tk = warp * (TT / WARPS) + u, t = tb + tk;
+            if (t >= t1) break;  // warp-uniform
+            float4 v[NV];
+            const float4* zr = zb + static_cast<size_t>(t) * F;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = __ldg(zr + 32 * i);
+            float m = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) m = fmaxf(fmaxf(fmaxf(v[i].x, v[i].y), fmaxf(v[i].z, v[i].w)), m);
+            m = warp_max(m);
+            const float ms = m * LOG2E;
+            float ssum = 0.f;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                v[i].x = exp2f(fmaf(v[i].x, LOG2E, -ms));
+                v[i].y = exp2f(fmaf(v[i].y, LOG2E, -ms));
+                v[i].z = exp2f(fmaf(v[i].z, LOG2E, -ms));
+                v[i].w = exp2f(fmaf(v[i].w, LOG2E, -ms));
+                ssum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+            }
+            ssum = warp_sum(ssum);
+            const float inv_s = 1.0f / ssum;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const float4 y = make_float4(v[i].x * inv_s, v[i].y * inv_s, v[i].z * inv_s, v[i].w * inv_s);
+                if (mode == POOL_MAX) {
+                    pool[i].x = fmaxf(pool[i].x, y.x); pool[i].y = fmaxf(pool[i].y, y.y);
+                    pool[i].z = fmaxf(pool[i].z, y.z); pool[i].w = fmaxf(pool[i].w, y.w);
+                } else {
+                    pool[i].x += y.x; pool[i].y += y.y; pool[i].z += y.z; pool[i].w += y.w;
+                }
+                tile[tk * F + ((lane + 32 * i) ^ (tk & 7))] = y;
+            }
+        }
+        __syncthreads();
+        // ---- every prototype's 32 tokens as one 128-byte segment: lane = token, a warp takes every 8th float4 column
+        {
+            const int t = tb + lane;
+            if (t < t1) {
+                for (int f = warp; f < F; f += WARPS) {
+                    const float4 y = tile[lane * F + (f ^ (lane & 7))];
+                    float* o = mb + static_cast<size_t>(4 * f) * HW + t;
+                    o[0] = y.x;
+                    o[HW] = y.y;
+                    o[2 * static_cast<size_t>(HW)] = y.z;
+                    o[3 * static_cast<size_t>(HW)] = y.w;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    float4* mine = reinterpret_cast<float4*>(s_pool + warp * P) + lane;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) mine[32 * i] = pool[i];
+    __syncthreads();
+    float* out = partial + (static_cast<size_t>(b) * chunks + chunk) * P;
+    for (int pp = threadIdx.x; pp < P; pp += blockDim.x) {
+        float a = s_pool[pp];
+        for (int wv = 1; wv < WARPS; ++wv) {
+            const float o = s_pool[wv * P + pp];
+            a = mode == POOL_MAX ? fmaxf(a, o) : a + o;
+        }
+        out[pp] = a;
+    }
+}
+
 // Register-resident variant for the common case (plain softmax, no map, P a multiple of 128 up to 1024): each lane
 // owns the same 4*NV prototypes of every token (NV float4 per lane, loaded once, coalesced 512 B per warp and
 // instruction), so the row max / sum are two warp reductions, the probabilities never leave registers and the running

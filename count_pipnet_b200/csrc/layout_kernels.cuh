@@ -1,7 +1,7 @@
 // Layout / gather kernels: NCHW<->NHWC transposes at the module boundary, and the im2col / pooling / subsample
 // gathers that turn the ResNet convolutions of features/resnet_features.py into rows for the tcgen05 GEMM.
 #pragma once
-#include "ptx.cuh"
+#include "device_utils.cuh"
 
 namespace cpn {
 
@@ -52,29 +52,58 @@ im2col_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, 
 }
 
 // im2col straight from the fp32 NCHW network input; column = c*k*k + kh*k + kw (the torch weight flattening).
+// A thread produces 8 consecutive columns of one row (16-byte stores of the hi and lo planes); the per-column tap offsets
+// come from a small shared-memory table instead of divisions per element.
 __global__ void __launch_bounds__(256)
 im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo,
                        int B, int C, int H, int W, int k, int stride, int pad, int Ho, int Wo, int Kpad) {
-    const long long total = static_cast<long long>(B) * Ho * Wo * Kpad;
+    extern __shared__ int s_tab[];  // [Kpad] offset c*H*W + kh*W + kw, then [Kpad] (kh << 16 | kw) or -1 for padding columns
+    int* s_off = s_tab;
+    int* s_khw = s_tab + Kpad;
     const int kk = k * k;
+    for (int col = threadIdx.x; col < Kpad; col += blockDim.x) {
+        if (col < C * kk) {
+            const int c = col / kk, r = col - c * kk;
+            const int kh = r / k, kw = r - kh * k;
+            s_off[col] = (c * H + kh) * W + kw;
+            s_khw[col] = (kh << 16) | kw;
+        } else {
+            s_off[col] = 0;
+            s_khw[col] = -1;
+        }
+    }
+    __syncthreads();
+    const int groups = Kpad >> 3;
+    const long long total = static_cast<long long>(B) * Ho * Wo * groups;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
-        const int col = static_cast<int>(i % Kpad);
-        const long long row = i / Kpad;
+        const int grp = static_cast<int>(i % groups);
+        const long long row = i / groups;
         const int wo = static_cast<int>(row % Wo);
-        const int ho = static_cast<int>((row / Wo) % Ho);
-        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
-        float v = 0.f;
-        if (col < C * kk) {
-            const int c = col / kk, r = col % kk;
-            const int kh = r / k, kw = r % k;
-            const int hi = ho * stride - pad + kh, wi = wo * stride - pad + kw;
-            if (hi >= 0 && hi < H && wi >= 0 && wi < W)
-                v = __ldg(x + ((static_cast<size_t>(b) * C + c) * H + hi) * W + wi);
+        const int rest = static_cast<int>(row / Wo);
+        const int ho = rest % Ho, b = rest / Ho;
+        const int h0 = ho * stride - pad, w0 = wo * stride - pad;
+        const float* xb = x + static_cast<size_t>(b) * C * H * W + static_cast<long long>(h0) * W + w0;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int col = grp * 8 + e;
+            const int khw = s_khw[col];
+            const int hi = h0 + (khw >> 16), wi = w0 + (khw & 0xffff);
+            v[e] = (khw >= 0 && hi >= 0 && hi < H && wi >= 0 && wi < W) ? __ldg(xb + s_off[col]) : 0.f;
         }
-        const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        out[i] = h;
-        if (out_lo != nullptr) out_lo[i] = __float2bfloat16_rn(v - __bfloat162float(h));
+        uint4 hi4, lo4;
+        hi4.x = pack_bf16x2(v[0], v[1]); hi4.y = pack_bf16x2(v[2], v[3]);
+        hi4.z = pack_bf16x2(v[4], v[5]); hi4.w = pack_bf16x2(v[6], v[7]);
+        const size_t o = static_cast<size_t>(row) * Kpad + grp * 8;
+        *reinterpret_cast<uint4*>(out + o) = hi4;
+        if (out_lo != nullptr) {
+            lo4.x = pack_bf16x2(v[0] - __uint_as_float(hi4.x << 16), v[1] - __uint_as_float(hi4.x & 0xffff0000u));
+            lo4.y = pack_bf16x2(v[2] - __uint_as_float(hi4.y << 16), v[3] - __uint_as_float(hi4.y & 0xffff0000u));
+            lo4.z = pack_bf16x2(v[4] - __uint_as_float(hi4.z << 16), v[5] - __uint_as_float(hi4.z & 0xffff0000u));
+            lo4.w = pack_bf16x2(v[6] - __uint_as_float(hi4.w << 16), v[7] - __uint_as_float(hi4.w & 0xffff0000u));
+            *reinterpret_cast<uint4*>(out_lo + o) = lo4;
+        }
     }
 }
 

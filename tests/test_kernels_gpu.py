@@ -357,10 +357,10 @@ def test_ln_im2col2(cuda_device, stride, H, W, C):
 
 
 @pytest.mark.parametrize("mode", [_lib.POOL_MAX, _lib.POOL_SUM])
-@pytest.mark.parametrize("P", [16, 768])
-def test_softmax_pool_and_map(cuda_device, mode, P):
+@pytest.mark.parametrize("P,HW,chunks", [(16, 100, 4), (768, 100, 4), (768, 333, 3), (128, 70, 2), (1024, 65, 1)])
+def test_softmax_pool_and_map(cuda_device, mode, P, HW, chunks):
     g = torch.Generator().manual_seed(P)
-    B, HW, chunks = 3, 100, 4
+    B = 3
     z = (torch.randn(B, HW, P, generator=g) * 3).to(cuda_device)
     partial = torch.empty(B, chunks, P, device=cuda_device)
     pmap = torch.empty(B, P, HW, device=cuda_device)
@@ -535,6 +535,22 @@ def test_conv_bn_act(cuda_device, B, H, W, Cin, Cout, k, kind):
 def test_conv3x3_tile_rows():
     assert ops.conv3x3_tile_rows(28, 28) == 4 and ops.conv3x3_tile_rows(56, 56) == 2
     assert ops.conv3x3_tile_rows(14, 14) == 0 and ops.conv3x3_tile_rows(8, 16) == 8
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 64, 64), (1, 37, 51), (3, 224, 224)])
+def test_im2col_nchw_stem(cuda_device, B, H, W):
+    """ResNet stem gather (conv 7x7, stride 2, pad 3 on the fp32 NCHW input) == F.unfold, K = 147 padded to 152."""
+    g = torch.Generator().manual_seed(H)
+    x = torch.randn(B, 3, H, W, generator=g).to(cuda_device)
+    Ho, Wo = (H + 6 - 7) // 2 + 1, (W + 6 - 7) // 2 + 1
+    hi = torch.full((B * Ho * Wo, 152), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    lo = torch.full((B * Ho * Wo, 152), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    ops.im2col_nchw_f32(x, hi, B, 3, H, W, 7, 2, 3, 152, out_lo=lo)
+    ref = F.unfold(x, kernel_size=7, stride=2, padding=3).transpose(1, 2).reshape(B * Ho * Wo, 147)
+    torch.cuda.synchronize()
+    assert torch.equal(hi[:, :147], ref.to(torch.bfloat16))
+    assert ((hi[:, :147].float() + lo[:, :147].float()) - ref).abs().max().item() < 1e-4
+    assert (hi[:, 147:] == 0).all() and (lo[:, 147:] == 0).all()
 
 
 def test_transposes(cuda_device):
