@@ -390,21 +390,14 @@ struct MlpLaunch {
     int grid;
 };
 
-template <int C, int CG, int EW = 8>
+template <int C, int CG>
 int launch_mlp_inst(const MlpLaunch& g, cudaStream_t st) {
-    using S = cpn::MlpCfg<C, CG, EW>;
-    auto kern = cpn::mlp_fused_kernel<C, CG, EW>;
+    using S = cpn::MlpCfg<C, CG>;
+    auto kern = cpn::mlp_fused_kernel<C, CG>;
     CPN_CUDA(ensure_smem(kern, S::TOTAL));
     CPN_CUDA(launch_pdl(kern, dim3(g.grid), dim3(S::THREADS), S::TOTAL, st, CG, g.tx, g.tw1, g.tw2, g.p));
     CPN_CUDA(cudaGetLastError());
     return 0;
-}
-
-// Epilogue warps of the fused MLP: 16 for the narrow stages (C <= 192), 8 at C = 384. CPN_MLP_EW=8 forces 8 (A/B runs).
-int mlp_ew(int C) {
-    static const int env = [] { const char* e = getenv("CPN_MLP_EW"); return e == nullptr ? 0 : atoi(e); }();
-    if (C == 384 || env == 8) return 8;
-    return 16;
 }
 
 int mlp_cg(int C) {
@@ -672,7 +665,6 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
         return fail("cpn_mlp_fused: missing operand");
     if ((reinterpret_cast<uintptr_t>(x) & 15) != 0) return fail("cpn_mlp_fused: x not 16-byte aligned");
     const int cg = mlp_cg(C);
-    const int ew = cg == 2 ? mlp_ew(C) : 8;
     const int n2 = C > 256 ? C / 2 : C;
     MlpLaunch g;
     memset(&g, 0, sizeof(g));
@@ -697,7 +689,7 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
     const int slots = num_sms() / cg;
     g.grid = cg * (g.p.num_tiles < slots ? g.p.num_tiles : slots);
     const double mc = static_cast<double>(M) * C;
-    set_info("mlp_fused", 16.0 * mc * C, 2.0 * mc + 8.0 * mc + 16.0 * C * C, "M=%d C=%d cg=%d ew=%d", M, C, cg, ew);
+    set_info("mlp_fused", 16.0 * mc * C, 2.0 * mc + 8.0 * mc + 16.0 * C * C, "M=%d C=%d cg=%d", M, C, cg);
 #ifdef CPN_DEV_KNOBS
     static long long* ts_dev = nullptr;  // dev only: CPN_MLP_TS=1 prints a clock64 trace of CTA 0's first tile
     static const bool want_ts = getenv("CPN_MLP_TS") != nullptr;
@@ -709,7 +701,6 @@ int cpn_mlp_fused(cpn_plan* plan, const void* y_bf16, const void* w1g, const voi
 #endif
     auto run = [=](cudaStream_t st) -> int {
         if (cg == 2) {
-            if (ew == 16) return C == 96 ? launch_mlp_inst<96, 2, 16>(g, st) : launch_mlp_inst<192, 2, 16>(g, st);
             switch (C) {
                 case 96: return launch_mlp_inst<96, 2>(g, st);
                 case 192: return launch_mlp_inst<192, 2>(g, st);

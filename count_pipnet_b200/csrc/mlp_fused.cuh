@@ -35,12 +35,7 @@ struct MlpParams {
     int dbg;              // -DCPN_DEV_KNOBS builds only (CPN_MLP_DBG): 1 = E1 skips its math, 2 = no MMAs, 4 = no weight loads
 };
 
-// EW = epilogue warps: 8, or 16 for the narrow stages (C <= 192), where the fc1 epilogue -- the same number of hidden
-// elements per launch at every stage -- is not hidden behind the GEMMs and two warps per scheduler leave its issue slots
-// two thirds empty (ncu, profiles/r02_ncu_full.md). With 16 the four warps of a TMEM lane quarter take 16 of a chunk's 64
-// hidden columns each; 640 threads cap the registers at 102 per thread, so the residual prefetch of the final epilogue
-// is one block deep.
-template <int C, int CG, int EWARPS = 8>
+template <int C, int CG>
 struct MlpCfg {
     static constexpr int KB1 = (C + 63) / 64;            // k-blocks of G1
     static constexpr int NJ = C / 16;                    // hidden chunks of 64 columns (4C / 64)
@@ -53,22 +48,17 @@ struct MlpCfg {
     static constexpr int W2_NS_BYTES = (N2 / CG) * 128;  // W2 rows staged by this CTA for one G2 instruction
     static constexpr int W2_BYTES = NSPLIT * W2_NS_BYTES;
     static constexpr int W_STAGE = ((W1_BYTES > W2_BYTES ? W1_BYTES : W2_BYTES) + 1023) / 1024 * 1024;
-    static constexpr int EW = EWARPS;
-    static constexpr int NGRP = EW / 4;                    // epilogue warps per TMEM lane quarter
-    static constexpr int CW = 64 / NGRP;                   // hidden columns of a chunk per warp (32 or 16)
-    static constexpr int NH = EW == 16 ? 4 : 3;            // the final epilogue's staging blocks (4 KB per warp) alias the H ring
+    static constexpr int NH = 3;
     static constexpr int H_SLOT = GEMM_BM * 128;
     static constexpr int BAR_BYTES = 256;
-    static constexpr int CB_SLOT = 2 * CW * 4;             // one chunk's coefficients of a warp: CW colsum + CW bias1
-    static constexpr int CB_BYTES = EW * 4 * CB_SLOT;      // per epilogue warp: ring of 4 chunks
+    static constexpr int CB_BYTES = 8 * 4 * 256;          // per epilogue warp: 4 chunks x (32 colsum + 32 bias1)
     static constexpr int BUDGET = 227 * 1024 - 1024 - BAR_BYTES - CB_BYTES - X_BYTES - NH * H_SLOT;
     static constexpr int NW = (BUDGET / W_STAGE) > 6 ? 6 : (BUDGET / W_STAGE);
     static constexpr int TOTAL = X_BYTES + NH * H_SLOT + NW * W_STAGE + BAR_BYTES + CB_BYTES + 1024;
     static constexpr int ACC1_COL = C;
     static constexpr int TMEM_COLS = (C + 128 <= 256) ? 256 : 512;
+    static constexpr int EW = 8;
     static constexpr int THREADS = 128 + 32 * EW;
-    static_assert(EW == 8 || EW == 16, "8 or 16 epilogue warps");
-    static_assert(EW * 4096 <= NH * H_SLOT, "final-epilogue staging must fit the H ring");
     static_assert(C % 32 == 0 && C <= 384, "acc2 (C columns) and two 64-column acc1 buffers must fit in 512 TMEM columns");
     static_assert(N2 % (16 * CG) == 0 && N2 <= 256, "UMMA N constraint");
     static_assert(W1_KB_BYTES % 1024 == 0 && W2_NS_BYTES % 1024 == 0, "operand blocks must keep the swizzle atom alignment");
@@ -76,12 +66,12 @@ struct MlpCfg {
     static_assert(NJ % 2 == 0, "acc1 buffer parity is tracked per tile");
 };
 
-template <int C, int CG, int EWARPS = 8>
-__global__ void __launch_bounds__(MlpCfg<C, CG, EWARPS>::THREADS, 1)
+template <int C, int CG>
+__global__ void __launch_bounds__(MlpCfg<C, CG>::THREADS, 1)
 mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w1,
                  const __grid_constant__ CUtensorMap tmap_w2, const MlpParams p) {
-    using S = MlpCfg<C, CG, EWARPS>;
-    constexpr int NW = S::NW, NH = S::NH, NJ = S::NJ, KB1 = S::KB1, EW = S::EW, NGRP = S::NGRP, CW = S::CW;
+    using S = MlpCfg<C, CG>;
+    constexpr int NW = S::NW, NH = S::NH, NJ = S::NJ, KB1 = S::KB1, EW = S::EW;
     const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;
 
     extern __shared__ uint8_t smem_raw[];
@@ -101,7 +91,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     uint64_t* a2_full = x_empty + 1;
     uint64_t* a2_empty = a2_full + 1;
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(a2_empty + 1);
-    uint8_t* cbs = reinterpret_cast<uint8_t*>(bars) + S::BAR_BYTES;  // [EW][4][2][CW] floats
+    uint8_t* cbs = reinterpret_cast<uint8_t*>(bars) + S::BAR_BYTES;  // [EW][4][2][32] floats
     static_assert((12 + 2 * NH + 8) * 8 + 8 <= S::BAR_BYTES, "barrier block too small");
 
     const int warp = threadIdx.x >> 5;
@@ -278,7 +268,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         // ------------------------------------------------------------ epilogue warps
         const int ew = warp - 4;
         const int q = warp & 3;    // TMEM lane quarter = 32-row block of the tile
-        const int half = ew >> 2;  // which CW of a chunk's 64 hidden columns / which 32-column blocks of the output
+        const int half = ew >> 2;  // which 32 of a chunk's 64 hidden columns / every other 32-column block of the output
         const uint32_t sw = static_cast<uint32_t>(lane & 7);
         const uint32_t row_off = static_cast<uint32_t>(q * 32 + lane) * 128u;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
@@ -288,13 +278,13 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         };
         // colsum / bias1 of this warp's 32 columns of a chunk: private ring of 4 slots x (32 + 32) floats, filled by
         // cp.async two chunks ahead (the L1 left next to ~220 KB of shared memory is too small to keep them)
-        const uint32_t cb_addr = ptx::smem_u32(cbs) + static_cast<uint32_t>(ew) * (4 * S::CB_SLOT);
+        const uint32_t cb_addr = ptx::smem_u32(cbs) + static_cast<uint32_t>(ew) * (4 * 256);
         auto cb_issue = [&](int jj) {
-            if (jj < NJ && lane < CW) {
-                const int col = jj * 64 + half * CW + lane;
-                const uint32_t d = cb_addr + static_cast<uint32_t>(jj & 3) * S::CB_SLOT + static_cast<uint32_t>(lane) * 4;
+            if (jj < NJ) {
+                const int col = jj * 64 + half * 32 + lane;
+                const uint32_t d = cb_addr + static_cast<uint32_t>(jj & 3) * 256 + static_cast<uint32_t>(lane) * 4;
                 ptx::cp_async4(d, p.colsum + col);
-                ptx::cp_async4(d + CW * 4, p.bias1 + col);
+                ptx::cp_async4(d + 128, p.bias1 + col);
             }
             ptx::cp_async_commit();
         };
@@ -340,12 +330,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 ptx::mbar_wait(&a1_full[buf], (g1 >> 1) & 1);
                 if (trace) tsp[1] = clock64();
                 ptx::tc_fence_after();
-                if (CW == 32) {
-                    ptx::tmem_ld32(lane_addr + S::ACC1_COL + buf * 64 + half * 32, r0);
-                } else {
-                    uint32_t(&r16)[16] = *reinterpret_cast<uint32_t(*)[16]>(r0);
-                    ptx::tmem_ld16(lane_addr + S::ACC1_COL + buf * 64 + half * 16, r16);
-                }
+                ptx::tmem_ld32(lane_addr + S::ACC1_COL + buf * 64 + half * 32, r0);
                 ptx::tmem_ld_wait();
                 if (trace) tsp[2] = clock64();
                 ptx::tc_fence_before();
@@ -356,20 +341,20 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                 ptx::mbar_wait(&h_empty[hslot], hphase ^ 1);  // the G2 that last read this slot has completed
                 if (trace) tsp[4] = clock64();
                 const uint32_t dst = ptx::smem_u32(hs + hslot * S::H_SLOT) + row_off;
-                const uint32_t cb = cb_addr + static_cast<uint32_t>(j & 3) * S::CB_SLOT;
+                const uint32_t cb = cb_addr + static_cast<uint32_t>(j & 3) * 256;
                 if (CPN_DBG(p.dbg, 1)) {
 #pragma unroll
-                    for (int i = 0; i < CW / 8; ++i)
-                        ptx::sts_u4(dst + ((static_cast<uint32_t>((CW / 8) * half + i) ^ sw) << 4),
+                    for (int i = 0; i < 4; ++i)
+                        ptx::sts_u4(dst + ((static_cast<uint32_t>(4 * half + i) ^ sw) << 4),
                                     make_uint4(r0[8 * i], r0[8 * i + 2], r0[8 * i + 4], r0[8 * i + 6]));
                 } else
 #pragma unroll
-                for (int i = 0; i < CW / 8; ++i) {
+                for (int i = 0; i < 4; ++i) {
                     const uint32_t* src = r0 + 8 * i;
                     const float4 s0 = ptx::lds_f4(cb + 32 * i);
                     const float4 s1 = ptx::lds_f4(cb + 32 * i + 16);
-                    const float4 b0 = ptx::lds_f4(cb + CW * 4 + 32 * i);
-                    const float4 b1 = ptx::lds_f4(cb + CW * 4 + 32 * i + 16);
+                    const float4 b0 = ptx::lds_f4(cb + 128 + 32 * i);
+                    const float4 b1 = ptx::lds_f4(cb + 128 + 32 * i + 16);
                     float2 v0 = make_float2(__uint_as_float(src[0]), __uint_as_float(src[1]));
                     float2 v1 = make_float2(__uint_as_float(src[2]), __uint_as_float(src[3]));
                     float2 v2 = make_float2(__uint_as_float(src[4]), __uint_as_float(src[5]));
@@ -382,7 +367,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                     const float2 y1 = gelu_sat2(v1);
                     const float2 y2 = gelu_sat2(v2);
                     const float2 y3 = gelu_sat2(v3);
-                    ptx::sts_u4(dst + ((static_cast<uint32_t>((CW / 8) * half + i) ^ sw) << 4),
+                    ptx::sts_u4(dst + ((static_cast<uint32_t>(4 * half + i) ^ sw) << 4),
                                 make_uint4(pack2(y0.x, y0.y), pack2(y1.x, y1.y), pack2(y2.x, y2.y), pack2(y3.x, y3.y)));
                 }
                 if (trace) tsp[5] = clock64();
@@ -401,13 +386,12 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
             // idle H ring) so that the residual loads and the stores are coalesced: lane l handles the 16-byte
             // column group l & 7 of rows 4 i + (l >> 3). The residual of the next block travels one block ahead.
             constexpr int NBLK = C / 32;
-            constexpr int NBMAX = (NBLK + NGRP - 1) / NGRP;
-            constexpr int RD = EW == 16 ? 1 : 2;  // residual blocks in flight (registers: 32 per block)
+            constexpr int NBMAX = (NBLK + 1) / 2;
             const uint32_t stg = ptx::smem_u32(hs) + static_cast<uint32_t>(ew) * 4096;
             const int row_w = (tile * CG + static_cast<int>(rank)) * GEMM_BM + q * 32;  // first row of this warp
             const int rsub = lane >> 3, cgrp = lane & 7;
             float* xbase = p.x + static_cast<size_t>(row_w) * C + cgrp * 4;
-            float4 res[RD][8];
+            float4 res[2][8];
             auto load_res = [&](int c, float4 (&dst)[8]) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -423,19 +407,15 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
             ptx::tc_fence_after();
 #pragma unroll
             for (int b = 0; b < NBMAX; ++b) {
-                const int c = half + NGRP * b;
+                const int c = half + 2 * b;
                 if (c < NBLK) {
-                    if (RD == 2) {
-                        if (c + NGRP < NBLK) load_res(c + NGRP, res[(b + 1) & (RD - 1)]);
-                    } else if (b > 0) {
-                        load_res(c, res[0]);
-                    }
+                    if (c + 2 < NBLK) load_res(c + 2, res[(b + 1) & 1]);
                     const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias2 + c * 32 + cgrp * 4));
                     const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + c * 32 + cgrp * 4));
                     uint32_t r0[32];
                     ptx::tmem_ld32(lane_addr + c * 32, r0);
                     ptx::tmem_ld_wait();
-                    if (c + NGRP >= NBLK) {
+                    if (c + 2 >= NBLK) {
                         ptx::tc_fence_before();
                         __syncwarp();
                         if (lane == 0) arrive(a2_empty);
@@ -450,7 +430,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
                         const int r = 4 * i + rsub;
                         const float4 a4 = ptx::lds_f4(stg + static_cast<uint32_t>(r) * 128 +
                                                       ((static_cast<uint32_t>(cgrp) ^ static_cast<uint32_t>(r & 7)) << 4));
-                        const float4 rr = res[b & (RD - 1)][i];
+                        const float4 rr = res[b & 1][i];
                         float4 v;
                         v.x = fmaf(a4.x + b4.x, s4.x, rr.x);
                         v.y = fmaf(a4.y + b4.y, s4.y, rr.y);
