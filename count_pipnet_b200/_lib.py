@@ -38,6 +38,7 @@ SIGNATURES = {
     "cpn_softmax_pool": [_vp, _vp, _vp, _f, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_softmax_pool_arg": [_vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_pool_argmax_reduce": [_vp, _vp, _vp, _i, _vp, _i, _i, _vp],
+    "cpn_softmax_pool_static": [_vp, _i, _vp, _i, _i, _i, _vp],  # no plan, no allocation (static device scratch)
     "cpn_topk_update": [_vp, _vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _vp, _vp],
     "cpn_eval_batch": [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "cpn_head_tail": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],

@@ -157,6 +157,18 @@ int cpn_softmax_pool_arg(cpn_plan* plan, const float* z, const float* gumbel, fl
 int cpn_pool_argmax_reduce(cpn_plan* plan, const float* partial, const int* partial_arg, int chunks, int* arg_out,
                            int B, int P, void* stream);
 
+/* Allocation-free variant of cpn_softmax_pool + the chunk fold of cpn_head_tail. It has NO counterpart in the reference;
+ * it was added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). Plain softmax over P per patch, then spatial max / sum:
+ * z [B,HW,P] fp32 -> pooled [B,P] fp32. The per-chunk partial results live in a static device array of
+ * CPN_SOFTMAX_POOL_STATIC_MAX_BYTES inside the library (held by every GPU that loads it, until exit) instead of a
+ * caller buffer: B * P * 4 bytes beyond that limit, or P > 3072, is rejected with an error. The call runs no cudaMalloc,
+ * cudaFree or allocating library routine and takes no plan. All calls share the array (it keeps the last call's
+ * contents; every entry that is read is overwritten first, so nothing needs clearing): calls on one stream are safe,
+ * calls that OVERLAP on the GPU (other streams / threads on the same device) race. */
+#define CPN_SOFTMAX_POOL_STATIC_MAX_BYTES (4u << 20)
+int cpn_softmax_pool_static(const float* z, int mode, float* pooled, int B, int HW, int P, void* stream);
+
 /* Running top-k images per prototype over a stream of batches (the search loop of util/vis_pipnet.py:209-271, which
  * runs one image per forward on the host): merges pooled [B,P] / argmax [B,P] (cpn_pool_argmax_reduce) of images
  * image_base .. image_base + B - 1 into top_val / top_img / top_tok [k,P] and top_cnt [P] (zero-initialised by the
