@@ -45,10 +45,12 @@ SIGNATURES = {
     "cpn_nhwc_to_nchw": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_nchw_to_nhwc": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "cpn_conv_bn_act": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "cpn_conv_bn_act_resb": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_im2col_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_im2col_nchw_f32": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "cpn_maxpool3s2": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_subsample2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "cpn_maxpool3s2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
 }
 
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2

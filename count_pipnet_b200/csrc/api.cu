@@ -1176,6 +1176,21 @@ int cpn_maxpool3s2(cpn_plan* plan, const float* x, float* out_f32, void* out_hi,
     });
 }
 
+int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream) {
+    if (x == nullptr || out == nullptr) return fail("cpn_maxpool3s2_bf16: missing operand");
+    if (C % 8 != 0 || ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) != 0)
+        return fail("cpn_maxpool3s2_bf16: C must be a multiple of 8 and the maps 16-byte aligned");
+    const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+    const int grid = gather_grid(static_cast<long long>(B) * Ho * Wo * (C / 8));
+    set_info("maxpool3s2", 0.0, 2.0 * B * H * W * C + 2.0 * B * Ho * Wo * C);
+    return submit(plan, stream, [=](cudaStream_t st) -> int {
+        cpn::maxpool3s2_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<uint4*>(out), B, H, W, C,
+                                                          Ho, Wo);
+        CPN_CUDA(cudaGetLastError());
+        return 0;
+    });
+}
+
 int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream) {
     if (C % 8 != 0) return fail("cpn_subsample2_bf16: C must be a multiple of 8");
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;

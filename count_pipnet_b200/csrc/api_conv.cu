@@ -37,6 +37,20 @@ int launch_conv_bn(const ConvLaunch& g, int bn, int cg, cudaStream_t st) {
     return fail("cpn_conv_bn_act: no instantiation for BN=%d cg=%d", bn, cg);
 }
 
+const char* epi_name(int epi, int relu) {
+    switch (epi) {
+        case cpn::CEPI_RELU_BF16: return relu ? "relu_bf16" : "bias_bf16";
+        case cpn::CEPI_RES_RELU: return "res_relu";
+        case cpn::CEPI_BIAS_F32: return "bias_f32";
+        case cpn::CEPI_RESB_RELU: return "resb_relu";
+        default: return "resb_relu_f32";
+    }
+}
+
+int conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const float* res_f32,
+                const void* res_bf16, float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize,
+                int relu, void* stream);
+
 }  // namespace
 
 extern "C" {
@@ -51,12 +65,33 @@ int cpn_conv3x3_tile_rows(int H, int W) {
 int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const float* res_f32,
                     float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
                     void* stream) {
+    return conv_bn_act(plan, x_bf16, w_bf16, bias, res_f32, nullptr, out_f32, out_bf16, B, H, W, Cin, Cout, ksize, relu, stream);
+}
+
+int cpn_conv_bn_act_resb(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const void* res_bf16,
+                         float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize, void* stream) {
+    if (res_bf16 == nullptr) return fail("cpn_conv_bn_act_resb: the bf16 residual is required");
+    return conv_bn_act(plan, x_bf16, w_bf16, bias, nullptr, res_bf16, out_f32, out_bf16, B, H, W, Cin, Cout, ksize, 1, stream);
+}
+
+}  // extern "C"
+
+namespace {
+
+int conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const float* res_f32,
+                const void* res_bf16, float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize,
+                int relu, void* stream) {
     if (x_bf16 == nullptr || w_bf16 == nullptr || bias == nullptr) return fail("cpn_conv_bn_act: missing operand");
     if (B <= 0 || H <= 0 || W <= 0) return fail("cpn_conv_bn_act: bad shape B=%d H=%d W=%d", B, H, W);
     if (ksize != 1 && ksize != 3) return fail("cpn_conv_bn_act: kernel size must be 1 or 3 (stride 1)");
     int epi;
-    if (res_f32 != nullptr && out_f32 != nullptr && out_bf16 != nullptr && relu) epi = cpn::CEPI_RES_RELU;
-    else if (res_f32 == nullptr && out_f32 == nullptr && out_bf16 != nullptr && relu) epi = cpn::CEPI_RELU_BF16;
+    if (res_bf16 != nullptr) {
+        if (out_bf16 != nullptr && out_f32 == nullptr) epi = cpn::CEPI_RESB_RELU;
+        else if (out_bf16 == nullptr && out_f32 != nullptr) epi = cpn::CEPI_RESB_RELU_F32;
+        else return fail("cpn_conv_bn_act_resb: exactly one of out_f32 / out_bf16");
+    }
+    else if (res_f32 != nullptr && out_f32 != nullptr && out_bf16 != nullptr && relu) epi = cpn::CEPI_RES_RELU;
+    else if (res_f32 == nullptr && out_f32 == nullptr && out_bf16 != nullptr) epi = cpn::CEPI_RELU_BF16;  // relu = 0: bias only
     else if (res_f32 == nullptr && out_f32 != nullptr && out_bf16 == nullptr && !relu) epi = cpn::CEPI_BIAS_F32;
     else return fail("cpn_conv_bn_act: unsupported output combination");
     const int bn_cands[3] = {256, 128, 64};
@@ -64,7 +99,7 @@ int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, cons
     if (M >= (1LL << 31)) return fail("cpn_conv_bn_act: too many rows");
     ConvLaunch g;
     memset(&g, 0, sizeof(g));
-    g.p.M = static_cast<int>(M); g.p.N = Cout; g.p.bias = bias;
+    g.p.M = static_cast<int>(M); g.p.N = Cout; g.p.bias = bias; g.p.relu = relu;
     const int K = ksize * ksize * Cin;
     if (ksize == 3) {
         if (Cin % 64 != 0) return fail("cpn_conv_bn_act: the implicit 3x3 conv needs Cin %% 64 == 0 (Cin=%d)", Cin);
@@ -108,14 +143,20 @@ int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, cons
     const cuuint64_t odims[2] = {static_cast<cuuint64_t>(Cout), static_cast<cuuint64_t>(M)};
     const cuuint32_t obox[2] = {32, 16};
     const cuuint64_t f32_stride[1] = {static_cast<cuuint64_t>(Cout) * 4}, bf16_stride[1] = {static_cast<cuuint64_t>(Cout) * 2};
-    if (epi == cpn::CEPI_RELU_BF16) {
+    if (epi == cpn::CEPI_RELU_BF16 || epi == cpn::CEPI_RESB_RELU) {
         if (make_tmap_tiled(&g.tout, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, out_bf16, odims, bf16_stride, obox, CU_TENSOR_MAP_SWIZZLE_64B) != 0)
             return -1;
         g.tres = g.tout; g.tout_bf16 = g.tout;
+        if (epi == cpn::CEPI_RESB_RELU &&
+            make_tmap_tiled(&g.tres, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, res_bf16, odims, bf16_stride, obox, CU_TENSOR_MAP_SWIZZLE_64B) != 0)
+            return -1;
     } else {
         if (make_tmap_tiled(&g.tout, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, out_f32, odims, f32_stride, obox, CU_TENSOR_MAP_SWIZZLE_128B) != 0)
             return -1;
         g.tres = g.tout; g.tout_bf16 = g.tout;
+        if (epi == cpn::CEPI_RESB_RELU_F32 &&
+            make_tmap_tiled(&g.tres, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, res_bf16, odims, bf16_stride, obox, CU_TENSOR_MAP_SWIZZLE_64B) != 0)
+            return -1;
         if (epi == cpn::CEPI_RES_RELU) {
             if (make_tmap_tiled(&g.tres, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, res_f32, odims, f32_stride, obox, CU_TENSOR_MAP_SWIZZLE_128B) != 0 ||
                 make_tmap_tiled(&g.tout_bf16, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, out_bf16, odims, bf16_stride, obox, CU_TENSOR_MAP_SWIZZLE_64B) != 0)
@@ -129,16 +170,19 @@ int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, cons
     const double mn = static_cast<double>(M) * Cout;
     set_info(ksize == 3 ? "conv_3x3" : "conv_1x1", 2.0 * mn * K,
              2.0 * (static_cast<double>(M) * Cin + static_cast<double>(Cout) * K) +
-                 mn * (epi == cpn::CEPI_RELU_BF16 ? 2.0 : (epi == cpn::CEPI_RES_RELU ? 10.0 : 4.0)),
+                 mn * (epi == cpn::CEPI_RELU_BF16 ? 2.0 : epi == cpn::CEPI_RES_RELU ? 10.0 : epi == cpn::CEPI_RESB_RELU ? 4.0
+                       : epi == cpn::CEPI_RESB_RELU_F32 ? 6.0 : 4.0),
              "B=%d H=%d W=%d Cin=%d Cout=%d k=%d BN=%d cg=%d rows/tile=%d epi=%s", B, H, W, Cin, Cout, ksize, bn, cg,
-             g.p.tile_rows, epi == cpn::CEPI_RELU_BF16 ? "relu_bf16" : (epi == cpn::CEPI_RES_RELU ? "res_relu" : "bias_f32"));
+             g.p.tile_rows, epi_name(epi, relu));
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         switch (epi) {
             case cpn::CEPI_RELU_BF16: return launch_conv_bn<cpn::CEPI_RELU_BF16>(g, bn, cg, st);
             case cpn::CEPI_RES_RELU: return launch_conv_bn<cpn::CEPI_RES_RELU>(g, bn, cg, st);
+            case cpn::CEPI_RESB_RELU: return launch_conv_bn<cpn::CEPI_RESB_RELU>(g, bn, cg, st);
+            case cpn::CEPI_RESB_RELU_F32: return launch_conv_bn<cpn::CEPI_RESB_RELU_F32>(g, bn, cg, st);
             default: return launch_conv_bn<cpn::CEPI_BIAS_F32>(g, bn, cg, st);
         }
     });
 }
 
-}  // extern "C"
+}  // namespace

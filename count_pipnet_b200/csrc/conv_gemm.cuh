@@ -11,6 +11,11 @@
 //   epilogues  CEPI_RELU_BF16   out_bf16 = relu(acc + bias)                              conv1 / conv2 + bn + relu
 //              CEPI_RES_RELU    out_f32 = relu(res_f32 + acc + bias), out_bf16 = bf16(out_f32)   conv3 + bn3 + identity + relu
 //              CEPI_BIAS_F32    out_f32 = acc + bias                                     downsample conv + bn (the identity)
+//              CEPI_RESB_RELU   out_bf16 = bf16(relu(res_bf16 + acc + bias))             the same block end on a bf16 residual
+//              CEPI_RESB_RELU_F32  out_f32 = relu(res_bf16 + acc + bias)                 ... of the last block (fp32 features)
+//   With the bf16 residual stream (programs_resnet.py, bf16 mode) a block end moves 2 + 2 bytes per element instead of
+//   4 + 4 + 2: these 1x1 convs are HBM-bound (K = 64 .. 512), 1.13 of the 2.86 ms of cfg3. p.relu = 0 turns
+//   CEPI_RELU_BF16 into the projection shortcut with a bf16 result.
 // Tiles of an implicit conv cover tile_rows = Ht * W < 128 accumulator rows; rows beyond are never loaded or stored
 // (TMA boxes of 16 rows, only the valid ones are issued).
 #pragma once
@@ -18,7 +23,8 @@
 
 namespace cpn {
 
-enum ConvEpi : int { CEPI_RELU_BF16 = 0, CEPI_RES_RELU = 1, CEPI_BIAS_F32 = 2 };
+enum ConvEpi : int { CEPI_RELU_BF16 = 0, CEPI_RES_RELU = 1, CEPI_BIAS_F32 = 2, CEPI_RESB_RELU = 3, CEPI_RESB_RELU_F32 = 4 };
+__host__ __device__ constexpr bool cepi_resb(int epi) { return epi == CEPI_RESB_RELU || epi == CEPI_RESB_RELU_F32; }
 
 struct ConvGemmParams {
     int M, N;
@@ -30,6 +36,7 @@ struct ConvGemmParams {
     int ht;             // image rows per tile (implicit)
     int tiles_per_img;  // H / ht (implicit)
     const float* bias;  // [N]
+    int relu;           // CEPI_RELU_BF16 only: 0 = no activation (projection shortcut)
 };
 
 template <int BN, int EPI, int CG>
@@ -40,7 +47,9 @@ struct ConvGemmCfg {
     static constexpr int EW = GEMM_EPI_WARPS;
     static constexpr int NCHUNK = BN / 32;
     static constexpr int STG_BLOCK = 32 * 128;        // fp32 chunk: 32 rows x 128 B; bf16 chunk: 32 rows x 64 B
-    static constexpr int STG_PER_WARP = 2 * STG_BLOCK;  // block 0: fp32 / bf16 output, block 1: bf16 copy (CEPI_RES_RELU)
+    // block 0: fp32 / bf16 output; block 1: bf16 copy (CEPI_RES_RELU), or bf16 output in its first half and the bf16
+    // residual chunk in its second half (CEPI_RESB_*)
+    static constexpr int STG_PER_WARP = 2 * STG_BLOCK;
     static constexpr int THREADS = 128 + 32 * EW;
     static constexpr int STAGING_BYTES = EW * STG_PER_WARP;
     static constexpr int BAR_BYTES = (2 * 8 + 4 + EW) * 8 + 16;
@@ -92,6 +101,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::prefetch_tmap(&tmap_res);
             ptx::prefetch_tmap(&tmap_out_bf16);
         }
+        if (cepi_resb(EPI)) ptx::prefetch_tmap(&tmap_res);
         for (int s = 0; s < STAGES; ++s) {
             ptx::mbar_init(&full_bar[s], 1);
             ptx::mbar_init(&empty_bar[s], 1);
@@ -204,6 +214,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if (half_ok[0]) ptx::tma_load_2d(stg_ptr, &tmap_res, col0, row0, rbar);
             if (half_ok[1]) ptx::tma_load_2d(stg_ptr + 2048, &tmap_res, col0, row0 + 16, rbar);
         };
+        constexpr int RESB_OFF = S::STG_BLOCK + 2048;  // bf16 residual chunk: 32 rows x 64 B, never read by a store
+        auto load_resb = [&](int col0, int row0) {  // lane 0
+            const uint32_t bytes = (half_ok[0] ? 1024u : 0u) + (half_ok[1] ? 1024u : 0u);
+            ptx::mbar_arrive_expect_tx(rbar, bytes);
+            if (half_ok[0]) ptx::tma_load_2d(stg_ptr + RESB_OFF, &tmap_res, col0, row0, rbar);
+            if (half_ok[1]) ptx::tma_load_2d(stg_ptr + RESB_OFF + 1024, &tmap_res, col0, row0 + 16, rbar);
+        };
         uint32_t g = 0;  // residual phases consumed by this warp
         int it = 0;
         for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
@@ -217,6 +234,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (lane == 0) load_res(col_tile + grp * 32, row0);  // travels while the MMAs run
                 __syncwarp();
             }
+            if (cepi_resb(EPI) && grp < S::NCHUNK) {
+                if (lane == 0) load_resb(col_tile + grp * 32, row0);
+                __syncwarp();
+            }
             ptx::mbar_wait(&tmem_full_bar[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -226,14 +247,68 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const bool last = c + 2 >= S::NCHUNK;
                 uint32_t r0[32];
                 ptx::tmem_ld32(taddr_row + c * 32, r0);
-                if (EPI != CEPI_RES_RELU) {
+                if (EPI != CEPI_RES_RELU && !cepi_resb(EPI)) {
                     if (lane == 0) ptx::bulk_wait_read<0>();  // the stores that last used the staging blocks have read them
                     __syncwarp();
                 }
                 ptx::tmem_ld_wait();
                 if (last) release_tmem(as);
-                if (EPI == CEPI_RELU_BF16) {
+                if (cepi_resb(EPI)) {
+                    // residual chunk (bf16, 64-byte swizzle) + acc + bias -> relu -> bf16 chunk or fp32 chunk
+                    const uint32_t sw2 = static_cast<uint32_t>((lane >> 1) & 3);
+                    const uint32_t rrow = stg + RESB_OFF + static_cast<uint32_t>(lane) * 64u;
+                    ptx::mbar_wait(rbar, g & 1);
+                    ++g;
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint4 rs = ptx::lds_u4(rrow + ((static_cast<uint32_t>(j) ^ sw2) << 4));
+                        const uint32_t rw[4] = {rs.x, rs.y, rs.z, rs.w};
+                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j));
+                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 8 * j + 4));
+                        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            v[8 * j + 2 * e] = fmaxf(__uint_as_float(r0[8 * j + 2 * e]) + bb[2 * e] + __uint_as_float(rw[e] << 16), 0.f);
+                            v[8 * j + 2 * e + 1] =
+                                fmaxf(__uint_as_float(r0[8 * j + 2 * e + 1]) + bb[2 * e + 1] + __uint_as_float(rw[e] & 0xffff0000u), 0.f);
+                        }
+                    }
+                    if (lane == 0) ptx::bulk_wait_read<0>();  // the store that last used the output block has read it
+                    __syncwarp();
+                    if (EPI == CEPI_RESB_RELU) {
+                        const uint32_t orow = stg + S::STG_BLOCK + static_cast<uint32_t>(lane) * 64u;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            ptx::sts_u4(orow + ((static_cast<uint32_t>(j) ^ sw2) << 4),
+                                        make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                                   pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7])));
+                    } else {
+                        const uint32_t sw = static_cast<uint32_t>(lane & 7);
+                        const uint32_t buf = stg + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            ptx::sts_u4(buf + ((static_cast<uint32_t>(j) ^ sw) << 4),
+                                        make_uint4(__float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]), __float_as_uint(v[4 * j + 2]),
+                                                   __float_as_uint(v[4 * j + 3])));
+                    }
+                    ptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (EPI == CEPI_RESB_RELU) {
+                            if (half_ok[0]) ptx::tma_store_2d(&tmap_out, stg_ptr + S::STG_BLOCK, col0, row0);
+                            if (half_ok[1]) ptx::tma_store_2d(&tmap_out, stg_ptr + S::STG_BLOCK + 1024, col0, row0 + 16);
+                        } else {
+                            if (half_ok[0]) ptx::tma_store_2d(&tmap_out, stg_ptr, col0, row0);
+                            if (half_ok[1]) ptx::tma_store_2d(&tmap_out, stg_ptr + 2048, col0, row0 + 16);
+                        }
+                        ptx::bulk_commit();
+                        if (!last) load_resb(col0 + 64, row0);  // this warp's next chunk (its block was read above)
+                    }
+                    __syncwarp();
+                } else if (EPI == CEPI_RELU_BF16) {
                     // 32 columns -> relu -> bf16, 32 rows x 64 B in the 64-byte TMA swizzle
+                    const float lo_clamp = p.relu ? 0.f : -INFINITY;
                     const uint32_t sw = static_cast<uint32_t>((lane >> 1) & 3);
                     const uint32_t row = stg + static_cast<uint32_t>(lane) * 64u;
 #pragma unroll
@@ -244,8 +319,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         uint32_t pk[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e)
-                            pk[e] = pack_bf16x2(fmaxf(__uint_as_float(r0[8 * j + 2 * e]) + bb[2 * e], 0.f),
-                                                fmaxf(__uint_as_float(r0[8 * j + 2 * e + 1]) + bb[2 * e + 1], 0.f));
+                            pk[e] = pack_bf16x2(fmaxf(__uint_as_float(r0[8 * j + 2 * e]) + bb[2 * e], lo_clamp),
+                                                fmaxf(__uint_as_float(r0[8 * j + 2 * e + 1]) + bb[2 * e + 1], lo_clamp));
                         ptx::sts_u4(row + ((static_cast<uint32_t>(j) ^ sw) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
                     }
                     ptx::fence_proxy_async();

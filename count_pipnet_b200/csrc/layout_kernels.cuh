@@ -138,6 +138,42 @@ maxpool3s2_kernel(const float* __restrict__ x, float* __restrict__ out_f32, __nv
     }
 }
 
+// The same pooling on a channels-last bf16 map, 8 channels (16 bytes) per thread. Rounding to bf16 is monotonic, so
+// max(bf16(a), bf16(b)) == bf16(max(a, b)): pooling the bf16 stem output gives the bits the fp32 pooling + rounding gives.
+__global__ void __launch_bounds__(256)
+maxpool3s2_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
+    const int c8 = C >> 3;
+    const long long total = static_cast<long long>(B) * Ho * Wo * c8;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int cc = static_cast<int>(i % c8);
+        const long long row = i / c8;
+        const int wo = static_cast<int>(row % Wo);
+        const int ho = static_cast<int>((row / Wo) % Ho);
+        const int b = static_cast<int>(row / (static_cast<long long>(Wo) * Ho));
+        const __nv_bfloat162 ninf = __float2bfloat162_rn(-INFINITY);
+        __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * 2 - 1 + kh;
+            if (hi < 0 || hi >= H) continue;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int wi = wo * 2 - 1 + kw;
+                if (wi < 0 || wi >= W) continue;
+                const uint4 v = __ldg(x + ((static_cast<size_t>(b) * H + hi) * W + wi) * c8 + cc);
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) m[e] = __hmax2(m[e], *reinterpret_cast<const __nv_bfloat162*>(&w4[e]));
+            }
+        }
+        uint4 o;
+        o.x = *reinterpret_cast<uint32_t*>(&m[0]); o.y = *reinterpret_cast<uint32_t*>(&m[1]);
+        o.z = *reinterpret_cast<uint32_t*>(&m[2]); o.w = *reinterpret_cast<uint32_t*>(&m[3]);
+        out[i] = o;
+    }
+}
+
 // out[b, ho, wo, :] = x[b, 2*ho, 2*wo, :]
 __global__ void __launch_bounds__(256)
 subsample2_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {

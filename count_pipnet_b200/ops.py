@@ -211,6 +211,13 @@ def conv_bn_act(x_bf16, w_bf16, bias, B, H, W, Cin, Cout, ksize, *, relu, res_f3
               ptr(out_bf16), B, H, W, Cin, Cout, int(ksize), int(bool(relu)), _stream())
 
 
+def conv_bn_act_resb(x_bf16, w_bf16, bias, res_bf16, B, H, W, Cin, Cout, ksize, *, out_f32=None, out_bf16=None, plan=None):
+    """Block-end conv + folded BN + bf16 identity + ReLU (bf16 residual stream): see cpn_conv_bn_act_resb in the header."""
+    _need_cuda(x_bf16, w_bf16, bias, res_bf16, out_f32, out_bf16)
+    _lib.call("cpn_conv_bn_act_resb", _ph(plan), ptr(x_bf16), ptr(w_bf16), ptr(bias), ptr(res_bf16), ptr(out_f32),
+              ptr(out_bf16), B, H, W, Cin, Cout, int(ksize), _stream())
+
+
 def im2col_bf16(x, out, B, H, W, Cc, k, stride, pad, Kpad, plan=None):
     _need_cuda(x, out)
     _lib.call("cpn_im2col_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, k, stride, pad, Kpad, _stream())
@@ -220,6 +227,11 @@ def im2col_nchw_f32(x, out, B, Cc, H, W, k, stride, pad, Kpad, out_lo=None, plan
     _need_cuda(x, out, out_lo)
     _lib.call("cpn_im2col_nchw_f32", _ph(plan), ptr(x), ptr(out), ptr(out_lo), B, Cc, H, W, k, stride, pad, Kpad,
               _stream())
+
+
+def maxpool3s2_bf16(x, out, B, H, W, Cc, plan=None):
+    _need_cuda(x, out)
+    _lib.call("cpn_maxpool3s2_bf16", _ph(plan), ptr(x), ptr(out), B, H, W, Cc, _stream())
 
 
 def maxpool3s2(x, B, H, W, Cc, out_f32=None, out_hi=None, out_lo=None, plan=None):

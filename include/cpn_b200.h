@@ -213,6 +213,7 @@ int cpn_nchw_to_nhwc(cpn_plan* plan, const float* x, float* out, int B, int HW, 
  * in; bias [Cout] = the folded BN shift. ksize = 1 (plain GEMM) or 3 (stride 1, pad 1: the nine taps are read from the
  * activation with 4-D TMA boxes, out-of-map rows / columns arrive as zeros = the padding). Output combinations:
  *   out_bf16 only, relu = 1                       out_bf16 = relu(conv + bias)                  conv1, conv2
+ *   out_bf16 only, relu = 0                       out_bf16 = conv + bias                        projection shortcut (bf16 stream)
  *   res_f32 + out_f32 + out_bf16, relu = 1        out_f32 = relu(res_f32 + conv + bias), out_bf16 = bf16(out_f32)   block end
  *   out_f32 only, relu = 0                        out_f32 = conv + bias                         projection shortcut
  * Cout % 64 == 0; ksize 3 needs Cin % 64 == 0 and cpn_conv3x3_tile_rows(H, W) > 0 (image rows per 128-row M tile; 0 =
@@ -221,6 +222,14 @@ int cpn_conv3x3_tile_rows(int H, int W);
 int cpn_conv_bn_act(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const float* res_f32,
                     float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
                     void* stream);
+/* The same conv + folded BN + identity + ReLU on a bf16 residual stream (bf16 mode of the ResNet program: a block end then
+ * moves 2 + 2 bytes per element instead of 4 + 4 + 2; these 1x1 convs are HBM-bound). res_bf16 [B*H*W, Cout] bf16 is the
+ * identity (features/resnet_features.py:110-115 `out += identity; out = self.relu(out)`); exactly one output:
+ *   out_bf16   = bf16(relu(res_bf16 + conv + bias))      every block but the last
+ *   out_f32    = relu(res_bf16 + conv + bias)            the last block (fp32 features for the head)
+ * cpn_conv_bn_act with out_bf16 only and relu = 0 gives the projection shortcut as bf16. */
+int cpn_conv_bn_act_resb(cpn_plan* plan, const void* x_bf16, const void* w_bf16, const float* bias, const void* res_bf16,
+                         float* out_f32, void* out_bf16, int B, int H, int W, int Cin, int Cout, int ksize, void* stream);
 
 /* im2col rows of a kxk convolution (pad, stride) over a channels-last bf16 map, K padded to Kpad with zeros:
  * out[(b,ho,wo), (kh*k+kw)*C + c] -- feeds cpn_gemm_bf16 for features/resnet_features.py convs. */
@@ -233,6 +242,9 @@ int cpn_im2col_nchw_f32(cpn_plan* plan, const float* x, void* out, void* out_lo,
  * (fp32, bf16 hi, bf16 lo) may be NULL. */
 int cpn_maxpool3s2(cpn_plan* plan, const float* x, float* out_f32, void* out_hi, void* out_lo, int B, int H, int W,
                    int C, void* stream);
+/* The same pooling on a channels-last bf16 map (the ResNet program's bf16 residual stream: rounding is monotonic, so the
+ * result equals bf16(maxpool(fp32 map))). C % 8 == 0. */
+int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
 /* Strided row subsample of a channels-last bf16 map (1x1 stride-2 downsample conv input, resnet_features.py:178). */
 int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
 

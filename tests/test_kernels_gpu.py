@@ -532,6 +532,56 @@ def test_conv_bn_act(cuda_device, B, H, W, Cin, Cout, k, kind):
         assert torch.equal(out16, out32.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,k,kind", [
+    (2, 28, 28, 256, 1024, 1, "resb"), (32, 28, 28, 512, 2048, 1, "resb"), (3, 56, 56, 64, 256, 1, "resb"),
+    (1, 28, 28, 64, 64, 3, "resb"), (2, 28, 28, 512, 2048, 1, "resb_f32"), (3, 8, 16, 64, 128, 3, "resb_f32"),
+    (2, 28, 28, 256, 512, 1, "bias_bf16"), (5, 28, 28, 1024, 2048, 1, "bias_bf16"), (2, 7, 7, 512, 512, 1, "resb")])
+def test_conv_bn_act_bf16_stream(cuda_device, B, H, W, Cin, Cout, k, kind):
+    """Block end on the bf16 residual stream (identity read as bf16, bf16 or fp32 result) and the bf16 projection
+    shortcut, vs F.conv2d on the same bf16 operands."""
+    g = torch.Generator().manual_seed(Cin + Cout + k + 1)
+    x = torch.randn(B, H, W, Cin, generator=g).to(cuda_device).to(torch.bfloat16)
+    w = (torch.randn(Cout, Cin, k, k, generator=g) / (Cin * k * k) ** 0.5).to(cuda_device).to(torch.bfloat16)
+    bias = torch.randn(Cout, generator=g).to(cuda_device)
+    wk = w.permute(0, 2, 3, 1).reshape(Cout, k * k * Cin).contiguous()
+    M = B * H * W
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=k // 2).permute(0, 2, 3, 1).reshape(M, Cout)
+    out32 = torch.full((M, Cout), float("nan"), device=cuda_device)
+    out16 = torch.full((M, Cout), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    if kind == "bias_bf16":
+        ops.conv_bn_act(x, wk, bias, B, H, W, Cin, Cout, k, relu=False, out_bf16=out16)
+        assert (ref < 0).any()  # the un-activated result keeps its negative values
+    else:
+        res = torch.randn(M, Cout, generator=g).to(cuda_device).to(torch.bfloat16)
+        ref = torch.relu(ref + res.float())
+        if kind == "resb":
+            ops.conv_bn_act_resb(x, wk, bias, res, B, H, W, Cin, Cout, k, out_bf16=out16)
+        else:
+            ops.conv_bn_act_resb(x, wk, bias, res, B, H, W, Cin, Cout, k, out_f32=out32)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    if kind == "resb_f32":
+        assert (out32 - ref).abs().max().item() <= 2e-3 * scale
+        assert torch.isnan(out16.float()).all()
+    else:
+        assert (out16.float() - ref).abs().max().item() <= 2.0 ** -8 * scale + 2e-3 * scale
+        assert torch.isnan(out32).all()
+
+
+@pytest.mark.parametrize("B,H,W,C", [(2, 112, 112, 64), (1, 37, 51, 64), (3, 8, 8, 128)])
+def test_maxpool3s2_bf16(cuda_device, B, H, W, C):
+    """bf16 pooling == bf16(fp32 pooling): rounding is monotonic (ResNet stem on the bf16 stream)."""
+    g = torch.Generator().manual_seed(H + C)
+    x32 = torch.randn(B, H, W, C, generator=g).to(cuda_device)
+    xb = x32.to(torch.bfloat16)
+    Ho, Wo = (H + 2 - 3) // 2 + 1, (W + 2 - 3) // 2 + 1
+    out = torch.full((B * Ho * Wo, C), float("nan"), device=cuda_device, dtype=torch.bfloat16)
+    ops.maxpool3s2_bf16(xb, out, B, H, W, C)
+    ref = F.max_pool2d(x32.permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1).reshape(B * Ho * Wo, C)
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref.to(torch.bfloat16))
+
+
 def test_conv3x3_tile_rows():
     assert ops.conv3x3_tile_rows(28, 28) == 4 and ops.conv3x3_tile_rows(56, 56) == 2
     assert ops.conv3x3_tile_rows(14, 14) == 0 and ops.conv3x3_tile_rows(8, 16) == 8
