@@ -41,7 +41,9 @@ constexpr int DW3_MAX_NS = 7;     // column strips per tile
 constexpr int DW3_SROW = 36;      // floats per pixel row of a warp's scratch (32 channels + 4: bank rotation)
 constexpr int DW3_WARPS = 16;      // 4 per scheduler
 constexpr int DW3_HALF = DW3_RB * DW3_TW / 2;            // pixels per output round
-constexpr int DW3_SCRATCH = DW3_HALF * DW3_SROW;         // floats per warp
+constexpr int DW3_BROW = 40;       // bf16 elements per pixel row of the bf16-mode scratch (32 channels + 8: 80-byte stride)
+constexpr int DW3_SCRATCH = DW3_RB * DW3_TW * DW3_BROW / 2;  // floats per warp: 28 x 80 B (>= the 14 x 144 B of fp32 mode)
+static_assert(DW3_SCRATCH >= DW3_HALF * DW3_SROW, "the scratch serves both modes");
 
 struct Dw3Params {
     const float* w49;   // [49, C]
@@ -186,8 +188,46 @@ dwconv7_v3_kernel(const __grid_constant__ CUtensorMap tmap_x, const Dw3Params p)
         __syncwarp();  // every lane has its inputs in registers (and has finished reading the scratch of its last item)
         if (lane == 0) ptx::mbar_arrive(&empty_bar[slot]);
 
-        // ------------------------------------------------------------ transpose through the warp's scratch, 2 x 14 pixels
         const int h_base = (t.rt * DW3_NB + k) * RB, w_base = (t.ct * p.NS + s) * TW;
+        if (!SPLIT) {
+            // -------------------------------------------------------- bf16 mode: ONE round through a bf16 scratch
+            // lane = channel rounds its 28 values and parks them as [pixel][32 x bf16] (pixel stride 80 B: the 16-byte
+            // reads of consecutive pixels rotate through the banks); lane L < 28 then owns pixel L: 64 contiguous bytes,
+            // already packed, and the sums over its 32 channels. Bit-identical to the two-round fp32 path below.
+            __nv_bfloat16* myb = reinterpret_cast<__nv_bfloat16*>(my);
+#pragma unroll
+            for (int q = 0; q < RB * TW; ++q) myb[q * DW3_BROW + lane] = __float2bfloat16_rn(acc[q / TW][q % TW]);
+            __syncwarp();
+            const int h = h_base + (lane >> 2), w = w_base + (lane & 3);
+            if (lane < RB * TW && h < p.H && w < p.W) {
+                uint32_t hw[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint4 f = *reinterpret_cast<const uint4*>(myb + lane * DW3_BROW + 8 * q);
+                    hw[4 * q] = f.x; hw[4 * q + 1] = f.y; hw[4 * q + 2] = f.z; hw[4 * q + 3] = f.w;
+                }
+                // the summation order of the two-round path: two chains per 16-channel half, halves added last
+                float sum[4] = {0.f, 0.f, 0.f, 0.f}, sq[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const float r0 = __uint_as_float(hw[q] << 16), r1 = __uint_as_float(hw[q] & 0xffff0000u);
+                    const int c4 = 2 * (q >> 3) + (q & 1);
+                    sum[c4] += r0 + r1;
+                    sq[c4] = fmaf(r0, r0, sq[c4]);
+                    sq[c4] = fmaf(r1, r1, sq[c4]);
+                }
+                const size_t pix = (static_cast<size_t>(t.b) * p.H + h) * p.W + w;
+                __nv_bfloat16* dst = p.out_hi + pix * p.C + t.grp * 32;
+                const uint32_t(&h0)[8] = *reinterpret_cast<const uint32_t(*)[8]>(&hw[0]);
+                const uint32_t(&h1)[8] = *reinterpret_cast<const uint32_t(*)[8]>(&hw[8]);
+                dw3_st256(dst, h0);
+                dw3_st256(dst + 16, h1);
+                reinterpret_cast<float2*>(p.stats)[pix * npart + t.grp] =
+                    make_float2((sum[0] + sum[1]) + (sum[2] + sum[3]), (sq[0] + sq[1]) + (sq[2] + sq[3]));
+            }
+            continue;
+        }
+        // ------------------------------------------------------------ fp32 mode: transpose through the scratch, 2 x 14 pixels
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             if (r == 1) __syncwarp();  // round 0 has been read
