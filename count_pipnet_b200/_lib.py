@@ -51,6 +51,7 @@ SIGNATURES = {
     "cpn_maxpool3s2": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_subsample2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_maxpool3s2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "cpn_preprocess_u8": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_float), C.POINTER(C.c_float), _vp],
 }
 
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
@@ -63,6 +64,7 @@ OTHER_SIGNATURES = {
     "cpn_last_error": ([], C.c_char_p),
     "cpn_plan_op_detail": ([_vp, _i], C.c_char_p),
     "cpn_conv3x3_tile_rows": ([_i, _i], C.c_int),  # a count, not a status
+    "cpn_preprocess_ws_ints": ([_i, _i, _i, _i], C.c_longlong),  # a size, not a status
 }
 
 

@@ -248,6 +248,18 @@ int cpn_maxpool3s2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, 
 /* Strided row subsample of a channels-last bf16 map (1x1 stride-2 downsample conv input, resnet_features.py:178). */
 int cpn_subsample2_bf16(cpn_plan* plan, const void* x, void* out, int B, int H, int W, int C, void* stream);
 
+/* ---- input pipeline -------------------------------------------------------------------- */
+/* The reference's evaluation transform `Compose([Resize((Ho, Wo)), ToTensor(), Normalize(mean, std)])` (util/data.py:381-385;
+ * same steps at :265-275, :296-307, :465-480, :522-531) for a batch of decoded RGB images of one size, bit-exact with
+ * Pillow's BILINEAR resize (Resample.c: widened triangle filter, 22-bit fixed-point coefficients, horizontal then vertical
+ * pass, each rounded to uint8) and torchvision's fp32 ToTensor / Normalize.
+ * src [B, Hs, Ws, 3] uint8 (device) -> out [B, 3, Ho, Wo] fp32 NCHW (device); mean3 / std3: three HOST floats each, read
+ * during the call; ws: device workspace of cpn_preprocess_ws_ints(Hs, Ws, Ho, Wo) ints (coefficient tables, rewritten by
+ * every call). Source sides up to 16384, down-scaling up to 64x. */
+long long cpn_preprocess_ws_ints(int Hs, int Ws, int Ho, int Wo);
+int cpn_preprocess_u8(cpn_plan* plan, const unsigned char* src, float* out, int* ws, int B, int Hs, int Ws, int Ho, int Wo,
+                      const float* mean3, const float* std3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

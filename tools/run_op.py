@@ -48,6 +48,15 @@ def main():
         fn = lambda: ops.dwconv7_stats_split(x, w49, b, hi, lo, stats)
         nbytes = x.numel() * 4 + hi.numel() * 4 + stats.numel() * 4
         flops = 2.0 * 49 * x.numel()
+    elif a.op == "preprocess":
+        # B decoded images of H x W (uint8 RGB) -> [B, 3, C, C] fp32 (C = target size): the reference's eval transform
+        from count_pipnet_b200.input_pipeline import EvalTransform
+        u8 = torch.randint(0, 256, (a.B, a.H, a.W, 3), generator=g, dtype=torch.uint8).to(dev)
+        tf = EvalTransform(a.C)
+        outp = torch.empty(a.B, 3, a.C, a.C, device=dev)
+        fn = lambda: tf(u8, outp)
+        nbytes = u8.numel() + outp.numel() * 4
+        flops = 0.0
     elif a.op == "gemm_ln":
         A = torch.randn(a.M, a.K, generator=g).to(dev).to(torch.bfloat16)
         Wt = (torch.randn(a.N, a.K, generator=g) / a.K ** 0.5).to(dev).to(torch.bfloat16)
