@@ -326,7 +326,7 @@ def run_ours(args, rank, world, local_rank):
     copy_stream = torch.cuda.Stream(device)
     main_stream = torch.cuda.current_stream(device)
 
-    def e2e_loop(n):
+    def e2e_loop(n, host=host, dev_in=dev_in, transform=None):
         ready = [torch.cuda.Event() for _ in range(2)]
         consumed = [torch.cuda.Event() for _ in range(2)]
         for e in consumed:
@@ -339,26 +339,48 @@ def run_ours(args, rank, world, local_rank):
                 ready[s].record(copy_stream)
             main_stream.wait_event(ready[s])
             with torch.no_grad():
-                _, pooled, out = model(dev_in[s], inference=True)
+                x_in = dev_in[s] if transform is None else transform(dev_in[s], dev_x)
+                _, pooled, out = model(x_in, inference=True)
             consumed[s].record(main_stream)
             host_logits.copy_(out, non_blocking=True)
             host_pooled.copy_(pooled, non_blocking=True)
         torch.cuda.synchronize()
 
-    e2e_loop(max(2, args.warmup))
-    barrier()
-    t0 = time.perf_counter()
-    e2e_loop(args.steps)
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=device)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * args.steps / float(e2e_s.item())
+    def timed_e2e(**kw):
+        e2e_loop(max(2, args.warmup), **kw)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_loop(args.steps, **kw)
+        e2e_s = torch.tensor([time.perf_counter() - t0], device=device)
+        if world > 1:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        return world * B * args.steps / float(e2e_s.item())
+
+    e2e_value = timed_e2e()
+    # The same loop fed the way the reference's loaders are fed -- decoded uint8 RGB images -- with the evaluation transform
+    # (Resize + ToTensor + Normalize, util/data.py:381-385) on the GPU (count_pipnet_b200/input_pipeline.py): a quarter of
+    # the host-to-device bytes per image at the same source size.
+    e2e_u8 = None
+    if not args.no_extras:
+        from count_pipnet_b200.input_pipeline import EvalTransform
+        src = (size * 8 // 7 + 7) // 8 * 8  # 224 -> 256, 192 -> 224, 448 -> 512: a typical stored size
+        gen = torch.Generator().manual_seed(3000 + rank)
+        host_u8 = [torch.randint(0, 256, (B, src, src, 3), generator=gen, dtype=torch.uint8).pin_memory() for _ in range(4)]
+        dev_u8 = [torch.empty(B, src, src, 3, dtype=torch.uint8, device=device) for _ in range(2)]
+        dev_x = torch.empty(B, 3, size, size, device=device)
+        e2e_u8 = {"value": timed_e2e(host=host_u8, dev_in=dev_u8, transform=EvalTransform(size)), "unit": UNIT,
+                  "h2d_bytes_per_step": B * src * src * 3, "d2h_bytes_per_step": B * (classes + protos) * 4,
+                  "what": f"pinned uint8 [B,{src},{src},3] batches -> H2D -> cpn_preprocess_u8 (Pillow-exact bilinear resize to "
+                          f"{size} + ToTensor + Normalize) -> forward -> D2H; random pixels"}
+        del host_u8, dev_u8, dev_x
 
     line = base_line(args, world, B)
     line.update({"value": value, "ms_per_step": ms_step, "dtype": "bf16" if args.precision == "bf16" else "bf16x3",
                  "clocks": clocks.summary(),
                  "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
                          "d2h_bytes_per_step": B * (classes + protos) * 4}})
+    if e2e_u8 is not None:
+        line["e2e_u8_input"] = e2e_u8
     line["config"].update({"precision_mode": args.precision, "parallelism": f"dp{world} (batch sharded, no data-path "
                            "collective except one packed logits+pooled all-gather)",
                            "l2_policy": f"inputs rotate over {nrot} resident batches ({nrot * in_bytes >> 20} MiB > L2)",

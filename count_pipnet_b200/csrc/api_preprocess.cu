@@ -10,7 +10,7 @@
 //     contracted into an FMA), rounded to 22-bit fixed point (normalize_coeffs_8bpc); a horizontal pass rounded and
 //     clipped to uint8, then a vertical pass rounded and clipped to uint8;
 //   * torchvision ToTensor (true fp32 division by 255) and Normalize ((x - mean) / std in fp32): one of 3 x 256 values, so
-//     a table per CTA.
+//     a table per call.
 // Layout: src [B, Hs, Ws, 3] uint8 (decoded RGB, channels last, what PIL / nvJPEG deliver) -> out [B, 3, Ho, Wo] fp32 NCHW
 // (what net.forward takes). The coefficient tables live in a caller-provided workspace: the library allocates nothing.
 #include "api_common.h"
@@ -67,17 +67,23 @@ __device__ __forceinline__ int pp_clip8(int acc) {
     return v < 0 ? 0 : (v > 255 ? 255 : v);
 }
 
+// ToTensor + Normalize of each of the 3 x 256 possible values, once per call (true fp32 divisions: ~30 instructions each --
+// far too many to repeat in every CTA of the resize kernel).
+__global__ void pp_lut_kernel(float* __restrict__ lut, float m0, float m1, float m2, float s0, float s1, float s2) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 768) return;
+    const int c = i >> 8, v = i & 255;
+    const float m = c == 0 ? m0 : (c == 1 ? m1 : m2), s = c == 0 ? s0 : (c == 1 ? s1 : s2);
+    lut[i] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(v), 255.0f), m), s);
+}
+
 // grid = (ceil(Wo / 128), Ho, B), 128 threads: one output pixel (3 channels) per thread.
 __global__ void __launch_bounds__(128)
 pp_resize_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ out, const int* __restrict__ xb,
-                           const int* __restrict__ xk, const int* __restrict__ yb, const int* __restrict__ yk, int Hs, int Ws,
-                           int Ho, int Wo, int kx, int ky, float m0, float m1, float m2, float s0, float s1, float s2) {
+                           const int* __restrict__ xk, const int* __restrict__ yb, const int* __restrict__ yk,
+                           const float* __restrict__ lut_g, int Hs, int Ws, int Ho, int Wo, int kx, int ky) {
     __shared__ float lut[3][256];
-    for (int i = threadIdx.x; i < 768; i += blockDim.x) {
-        const int c = i >> 8, v = i & 255;
-        const float m = c == 0 ? m0 : (c == 1 ? m1 : m2), s = c == 0 ? s0 : (c == 1 ? s1 : s2);
-        lut[c][v] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(v), 255.0f), m), s);
-    }
+    for (int i = threadIdx.x; i < 768; i += blockDim.x) (&lut[0][0])[i] = __ldg(lut_g + i);
     __syncthreads();
     const int ox = blockIdx.x * blockDim.x + threadIdx.x;
     const int oy = blockIdx.y, b = blockIdx.z;
@@ -116,7 +122,8 @@ extern "C" {
 
 long long cpn_preprocess_ws_ints(int Hs, int Ws, int Ho, int Wo) {
     if (Hs <= 0 || Ws <= 0 || Ho <= 0 || Wo <= 0) return 0;
-    return 2LL * Wo + static_cast<long long>(Wo) * pp_ksize(Ws, Wo) + 2LL * Ho + static_cast<long long>(Ho) * pp_ksize(Hs, Ho);
+    return 2LL * Wo + static_cast<long long>(Wo) * pp_ksize(Ws, Wo) + 2LL * Ho + static_cast<long long>(Ho) * pp_ksize(Hs, Ho) +
+           768;  // + the 3 x 256 fp32 table of ToTensor + Normalize
 }
 
 int cpn_preprocess_u8(cpn_plan* plan, const unsigned char* src, float* out, int* ws, int B, int Hs, int Ws, int Ho, int Wo,
@@ -132,13 +139,15 @@ int cpn_preprocess_u8(cpn_plan* plan, const unsigned char* src, float* out, int*
     int* xk = xb + 2 * Wo;
     int* yb = xk + static_cast<size_t>(Wo) * kx;
     int* yk = yb + 2 * Ho;
+    float* lut = reinterpret_cast<float*>(yk + static_cast<size_t>(Ho) * ky);
     const float m0 = mean3[0], m1 = mean3[1], m2 = mean3[2], s0 = std3[0], s1 = std3[1], s2 = std3[2];  // host values, read now
     set_info("preprocess_u8", 0.0, 3.0 * B * Hs * Ws + 12.0 * B * Ho * Wo, "B=%d %dx%d -> %dx%d taps=%dx%d", B, Hs, Ws, Ho, Wo, ky, kx);
     const dim3 grid((Wo + 127) / 128, Ho, B);
     return submit(plan, stream, [=](cudaStream_t st) -> int {
         pp_coeffs_kernel<<<(Wo + 127) / 128, 128, 0, st>>>(Ws, Wo, kx, xb, xk);
         pp_coeffs_kernel<<<(Ho + 127) / 128, 128, 0, st>>>(Hs, Ho, ky, yb, yk);
-        pp_resize_normalize_kernel<<<grid, 128, 0, st>>>(src, out, xb, xk, yb, yk, Hs, Ws, Ho, Wo, kx, ky, m0, m1, m2, s0, s1, s2);
+        pp_lut_kernel<<<3, 256, 0, st>>>(lut, m0, m1, m2, s0, s1, s2);
+        pp_resize_normalize_kernel<<<grid, 128, 0, st>>>(src, out, xb, xk, yb, yk, lut, Hs, Ws, Ho, Wo, kx, ky);
         CPN_CUDA(cudaGetLastError());
         return 0;
     });
