@@ -11,7 +11,7 @@ for c in "$@"; do
 import json
 try:
     d = json.loads(open("gpurun_out/r02_bench_${c}_n${N}.json").read().strip().splitlines()[-1])
-    print({k: d.get(k) for k in ("value", "ms_per_step", "n_gpus")}, "e2e", d["e2e"]["value"], "fp32", (d.get("fp32_mode") or {}).get("value"), d["clocks"])
+    print({k: d.get(k) for k in ("value", "ms_per_step", "n_gpus")}, "e2e", d["e2e"]["value"], "e2e_u8", (d.get("e2e_u8_input") or {}).get("value"), "fp32", (d.get("fp32_mode") or {}).get("value"), d["clocks"])
 except Exception as e:
     print("no line:", e)
 PY
