@@ -52,6 +52,11 @@ SIGNATURES = {
     "cpn_subsample2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_maxpool3s2_bf16": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "cpn_preprocess_u8": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_float), C.POINTER(C.c_float), _vp],
+    # training side of the head (no plan argument)
+    "cpn_pipnet_loss": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
+    "cpn_scale_unless_one": [_vp, _ll, _vp, _vp],
+    "cpn_softmax_pool_nchw": [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp],
+    "cpn_softmax_pool_nchw_bwd": [_vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp],
 }
 
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
@@ -65,6 +70,8 @@ OTHER_SIGNATURES = {
     "cpn_plan_op_detail": ([_vp, _i], C.c_char_p),
     "cpn_conv3x3_tile_rows": ([_i, _i], C.c_int),  # a count, not a status
     "cpn_preprocess_ws_ints": ([_i, _i, _i, _i], C.c_longlong),  # a size, not a status
+    "cpn_pipnet_loss_ws_floats": ([_i, _i, _i], C.c_longlong),
+    "cpn_softmax_pool_nchw_ws_floats": ([_i, _i, _i], C.c_longlong),
 }
 
 

@@ -1,0 +1,133 @@
+// C-ABI entry points of the training side of the prototype head (include/cpn_b200.h, "training" section): the PIP-Net
+// losses with their gradients (reference pipnet/train.py:165-243, 253-265) and softmax + pooling forward / backward on
+// the NCHW map of the autograd path (pipnet/pipnet.py:31-35, pipnet/count_pipnet.py:356-360, 88). Nothing is recorded
+// in plans here: a training step changes its weights every iteration and is not replayed.
+#include "api_common.h"
+#include "train_kernels.cuh"
+
+using namespace cpn_api;
+
+namespace {
+
+inline int tiles_of(int HW) { return (HW + cpn::TRAIN_TX - 1) / cpn::TRAIN_TX; }
+inline int tanh_blocks(int P) { return (P + 127) / 128; }
+
+struct LossWs {  // layout of the caller's workspace, in floats
+    long long align, tanh, row_loss, row_gmult, row_correct, total;
+};
+LossWs loss_ws(int B, int P, int HW) {
+    LossWs w;
+    w.align = 0;
+    w.tanh = w.align + static_cast<long long>(B) * tiles_of(HW);
+    w.row_loss = w.tanh + 2LL * tanh_blocks(P);
+    w.row_gmult = w.row_loss + 2LL * B;
+    w.row_correct = w.row_gmult + 2LL * B;
+    w.total = w.row_correct + 2LL * B;
+    return w;
+}
+
+}  // namespace
+
+extern "C" long long cpn_pipnet_loss_ws_floats(int B, int P, int HW) {
+    if (B <= 0 || P <= 0 || HW <= 0) return -1;
+    return loss_ws(B, P, HW).total;
+}
+
+extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled, const float* out, const long long* ys,
+                               const float* norm_mult, int B, int P, int HW, int K, float align_w, float tanh_w,
+                               float class_w, float tanh_coeff, float eps_tanh, int pretrain, int finetune,
+                               int use_log1p, float* grad_pf, float* grad_pooled, float* grad_out, float* result,
+                               float* workspace, void* stream) {
+    if (proto_features == nullptr || pooled == nullptr || result == nullptr || workspace == nullptr)
+        return fail("cpn_pipnet_loss: missing operand");
+    if (B <= 0 || B > 32767 || P <= 0 || HW <= 0) return fail("cpn_pipnet_loss: bad B=%d P=%d HW=%d", B, P, HW);
+    if (!pretrain) {
+        if (out == nullptr || ys == nullptr || K <= 0) return fail("cpn_pipnet_loss: out / ys / K needed unless pretrain");
+        if (use_log1p && norm_mult == nullptr) return fail("cpn_pipnet_loss: norm_mult needed for log1p(out^m)");
+    }
+    if (pretrain && finetune) return fail("cpn_pipnet_loss: pretrain and finetune exclude each other");
+    if (finetune && (grad_pf != nullptr || grad_pooled != nullptr))
+        return fail("cpn_pipnet_loss: the fine-tuning loss has no align / tanh term (train.py:224-225); pass NULL for "
+                    "grad_pf and grad_pooled");
+    const LossWs w = loss_ws(B, P, HW);
+    const int tiles = tiles_of(HW);
+    const double n_patches = static_cast<double>(B) * HW;
+    const float align_eps = 1e-12f;  // align_loss's own default (train.py:254), not calculate_loss's EPS
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    set_info("pipnet_loss", 4.0 * B * P * HW, (grad_pf ? 16.0 : 8.0) * B * P * HW);
+
+    cpn::align_loss_kernel<<<dim3(tiles, B), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0, st>>>(
+        proto_features, grad_pf, workspace + w.align, B, P, HW, align_eps,
+        static_cast<float>(-0.5 * align_w / n_patches));
+    CPN_CUDA(cudaGetLastError());
+    cpn::tanh_loss_kernel<<<dim3(tanh_blocks(P), 2), 128, 0, st>>>(pooled, grad_pooled, workspace + w.tanh, B, P,
+                                                                    tanh_coeff, eps_tanh,
+                                                                    static_cast<float>(-0.5 * tanh_w / P));
+    CPN_CUDA(cudaGetLastError());
+    if (!pretrain) {
+        cpn::class_loss_kernel<<<2 * B, 128, 0, st>>>(out, ys, norm_mult, use_log1p, grad_out, workspace + w.row_loss,
+                                                      workspace + w.row_gmult, workspace + w.row_correct, B, K,
+                                                      static_cast<float>(class_w / (2.0 * B)));
+        CPN_CUDA(cudaGetLastError());
+    }
+    cpn::loss_finalize_kernel<<<1, 256, 0, st>>>(workspace + w.align, B * tiles, workspace + w.tanh, tanh_blocks(P),
+                                                 workspace + w.row_loss, workspace + w.row_gmult,
+                                                 workspace + w.row_correct, 2 * B, static_cast<float>(n_patches),
+                                                 static_cast<float>(P), align_w, tanh_w, class_w, pretrain, finetune,
+                                                 result);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int cpn_scale_unless_one(float* buf, long long n, const float* scale, void* stream) {
+    if (buf == nullptr || scale == nullptr || n < 0) return fail("cpn_scale_unless_one: bad operand");
+    if (n == 0) return 0;
+    long long blocks = (n + 1023) / 1024;
+    const long long cap = 8LL * num_sms();
+    if (blocks > cap) blocks = cap;
+    cpn::scale_unless_one_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(buf, n, scale);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" long long cpn_softmax_pool_nchw_ws_floats(int N, int P, int HW) {
+    if (N <= 0 || P <= 0 || HW <= 0) return -1;
+    return 2LL * N * tiles_of(HW) * P;  // values, then indices (int32 in the same words)
+}
+
+extern "C" int cpn_softmax_pool_nchw(const float* z, int mode, float* proto_features, float* pooled, int* argmax, int N,
+                                     int P, int HW, float* workspace, void* stream) {
+    if (z == nullptr || proto_features == nullptr || pooled == nullptr || workspace == nullptr)
+        return fail("cpn_softmax_pool_nchw: missing operand");
+    if (mode != CPN_POOL_MAX && mode != CPN_POOL_SUM) return fail("cpn_softmax_pool_nchw: mode %d", mode);
+    if (mode == CPN_POOL_MAX && argmax == nullptr) return fail("cpn_softmax_pool_nchw: max pooling needs argmax [N, P]");
+    if (N <= 0 || N > 65535 || P <= 0 || HW <= 0) return fail("cpn_softmax_pool_nchw: bad N=%d P=%d HW=%d", N, P, HW);
+    const int tiles = tiles_of(HW);
+    float* part_val = workspace;
+    int* part_idx = reinterpret_cast<int*>(workspace + static_cast<size_t>(N) * tiles * P);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    set_info("softmax_pool_nchw", 0.0, 8.0 * N * P * HW);
+    cpn::softmax_pool_nchw_kernel<<<dim3(tiles, N), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0, st>>>(
+        z, proto_features, part_val, mode == CPN_POOL_MAX ? part_idx : nullptr, mode == CPN_POOL_SUM, P, HW);
+    CPN_CUDA(cudaGetLastError());
+    cpn::pool_fold_nchw_kernel<<<dim3((P + 127) / 128, N), 128, 0, st>>>(part_val, part_idx, mode == CPN_POOL_SUM, pooled,
+                                                                        argmax, P, tiles);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int cpn_softmax_pool_nchw_bwd(const float* proto_features, const float* grad_pf, const float* grad_pooled,
+                                         const int* argmax, int mode, float* grad_z, int N, int P, int HW,
+                                         void* stream) {
+    if (proto_features == nullptr || grad_z == nullptr) return fail("cpn_softmax_pool_nchw_bwd: missing operand");
+    if (mode != CPN_POOL_MAX && mode != CPN_POOL_SUM) return fail("cpn_softmax_pool_nchw_bwd: mode %d", mode);
+    if (mode == CPN_POOL_MAX && grad_pooled != nullptr && argmax == nullptr)
+        return fail("cpn_softmax_pool_nchw_bwd: max pooling needs the forward's argmax");
+    if (N <= 0 || N > 65535 || P <= 0 || HW <= 0) return fail("cpn_softmax_pool_nchw_bwd: bad N=%d P=%d HW=%d", N, P, HW);
+    set_info("softmax_pool_nchw_bwd", 0.0, (grad_pf ? 12.0 : 8.0) * N * P * HW);
+    cpn::softmax_pool_nchw_bwd_kernel<<<dim3(tiles_of(HW), N), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0,
+                                        static_cast<cudaStream_t>(stream)>>>(proto_features, grad_pf, grad_pooled, argmax,
+                                                                             mode == CPN_POOL_SUM, grad_z, P, HW);
+    CPN_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,394 @@
+// Training-side kernels of the prototype head: the PIP-Net losses with their gradients in
+// one pass over the prototype map, and softmax + spatial pooling forward / backward on the NCHW map the composed
+// (autograd) backbone hands over. HBM-bound fp32 work: coalesced along the spatial axis, fixed-order reductions (two
+// runs give the same bits), no atomics.
+//
+//   reference                                            kernel
+//   pipnet/train.py:253-265 align_loss (both directions)  align_loss_kernel
+//   pipnet/train.py:198-201 tanh loss                      tanh_loss_kernel
+//   pipnet/train.py:216-222 log1p(out^m) + log_softmax
+//     + NLLLoss(mean), :233-235 accuracy                   class_loss_kernel
+//   pipnet/train.py:212-229 weighting of the terms         loss_finalize_kernel
+//   pipnet/pipnet.py:96,105 Softmax(dim=1) + max pool,
+//     pipnet/count_pipnet.py:88 spatial sum                softmax_pool_nchw_kernel, pool_fold_nchw_kernel
+//   their autograd backward                                softmax_pool_nchw_bwd_kernel
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+#include "device_utils.cuh"
+
+namespace cpn {
+
+constexpr int TRAIN_TX = 32;  // spatial positions per CTA (one coalesced 128-byte row segment per channel)
+constexpr int TRAIN_TY = 32;  // channel groups per CTA: 1024 threads, two CTAs per SM, so that the second pass of a
+                              // CTA (32 positions x P channels x 2 tensors) is still in L2 when it is read again
+
+// Sum over the TY partials of one spatial position in a fixed order (ty = 0 .. TY-1).
+__device__ __forceinline__ float column_sum(const float (*s)[TRAIN_TX + 1], int tx) {
+    float d = 0.f;
+#pragma unroll 8
+    for (int j = 0; j < TRAIN_TY; ++j) d += s[j][tx];
+    return d;
+}
+
+// ---- align loss -----------------------------------------------------------------------------------------------------
+// pf [2B, P, HW]: view 1 = images [0, B), view 2 = images [B, 2B). For patch n = (b, hw): d_n = sum_c pf1 * pf2,
+// loss = -mean_n log(d_n + eps) (the two directions of train.py:173 have the same value); d loss / d pf1 = grad_scale *
+// pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
+// grid = (ceil(HW / 32), B), block = (32, 32). partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
+__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+    align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial, int B, int P,
+                      int HW, float eps, float grad_scale) {
+    __shared__ float s_dot[TRAIN_TY][TRAIN_TX + 1];
+    __shared__ float s_coef[TRAIN_TX];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int b = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
+    const bool ok = hw < HW;
+    const size_t img = static_cast<size_t>(P) * HW;
+    const size_t off1 = static_cast<size_t>(b) * img + hw, off2 = off1 + static_cast<size_t>(B) * img;
+    const float* p1 = pf + off1;
+    const float* p2 = pf + off2;
+    float acc = 0.f;
+    if (ok) {
+        int c = ty;
+        for (; c + 3 * TRAIN_TY < P; c += 4 * TRAIN_TY) {
+            float a[4], v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                a[j] = p1[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+                v[j] = p2[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc = fmaf(a[j], v[j], acc);
+        }
+        for (; c < P; c += TRAIN_TY) acc = fmaf(p1[static_cast<size_t>(c) * HW], p2[static_cast<size_t>(c) * HW], acc);
+    }
+    s_dot[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0) {
+        const float d = column_sum(s_dot, tx) + eps;
+        s_coef[tx] = ok ? grad_scale / d : 0.f;
+        const float l = warp_sum(ok ? -logf(d) : 0.f);
+        if (tx == 0) partial[static_cast<size_t>(b) * gridDim.x + blockIdx.x] = l;
+    }
+    if (grad == nullptr) return;
+    __syncthreads();
+    if (!ok) return;
+    const float k = s_coef[tx];
+    float* g1 = grad + off1;
+    float* g2 = grad + off2;
+    int c = ty;
+    for (; c + 3 * TRAIN_TY < P; c += 4 * TRAIN_TY) {
+        float a[4], v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            a[j] = p1[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+            v[j] = p2[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            __stcs(g1 + static_cast<size_t>(c + j * TRAIN_TY) * HW, k * v[j]);
+            __stcs(g2 + static_cast<size_t>(c + j * TRAIN_TY) * HW, k * a[j]);
+        }
+    }
+    for (; c < P; c += TRAIN_TY) {
+        const float a = p1[static_cast<size_t>(c) * HW], v = p2[static_cast<size_t>(c) * HW];
+        __stcs(g1 + static_cast<size_t>(c) * HW, k * v);
+        __stcs(g2 + static_cast<size_t>(c) * HW, k * a);
+    }
+}
+
+// ---- tanh loss ------------------------------------------------------------------------------------------------------
+// pooled [2B, P]; for each view: t_p = tanh(sum_b coeff * pooled[b, p]), loss term = log(t_p + eps).
+// grid = (ceil(P / 128), 2), block = 128. partial [2 * gridDim.x] = per-CTA sum of log(t + eps).
+// d loss / d pooled[b, p] = grad_scale * coeff * (1 - t^2) / (t + eps), grad_scale = -tanh_weight / (2 P).
+__global__ void __launch_bounds__(128)
+    tanh_loss_kernel(const float* __restrict__ pooled, float* __restrict__ grad, float* __restrict__ partial, int B, int P,
+                     float coeff, float eps, float grad_scale) {
+    __shared__ float s_part[4];
+    const int view = blockIdx.y, p = blockIdx.x * 128 + threadIdx.x;
+    const float* src = pooled + static_cast<size_t>(view) * B * P + p;
+    float l = 0.f;
+    if (p < P) {
+        float s = 0.f;
+        for (int b = 0; b < B; ++b) s = __fadd_rn(s, __fmul_rn(coeff, src[static_cast<size_t>(b) * P]));
+        const float t = tanhf(s);
+        l = logf(t + eps);
+        if (grad != nullptr) {
+            const float g = grad_scale * coeff * (1.f - t * t) / (t + eps);
+            float* dst = grad + static_cast<size_t>(view) * B * P + p;
+            for (int b = 0; b < B; ++b) dst[static_cast<size_t>(b) * P] = g;
+        }
+    }
+    l = warp_sum(l);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l;
+    __syncthreads();
+    if (threadIdx.x == 0) partial[view * gridDim.x + blockIdx.x] = (s_part[0] + s_part[1]) + (s_part[2] + s_part[3]);
+}
+
+// ---- classification loss --------------------------------------------------------------------------------------------
+// out [2B, K], ys [B] (labels of the pairs: train.py:169 ys = cat(ys1, ys1)), mult = the classifier's
+// normalization_multiplier (one float on the device). v = use_log1p ? log1p(out^mult) : out; loss_i = -log_softmax(v)[y].
+// One CTA of 128 threads per row. Writes grad_out (scaled by grad_scale = class_weight / 2B), and per row: the loss,
+// the multiplier's gradient, whether arg-max(out) == y (first index on ties, as torch.argmax on CUDA).
+struct ValIdx {
+    float v;
+    int i;
+};
+__device__ __forceinline__ ValIdx better(ValIdx a, ValIdx b) {  // larger value, then lower index
+    return (b.v > a.v || (b.v == a.v && b.i < a.i)) ? b : a;
+}
+__device__ __forceinline__ ValIdx warp_argmax(ValIdx a) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ValIdx b;
+        b.v = __shfl_xor_sync(0xffffffffu, a.v, o);
+        b.i = __shfl_xor_sync(0xffffffffu, a.i, o);
+        a = better(a, b);
+    }
+    return a;
+}
+
+__global__ void __launch_bounds__(128)
+    class_loss_kernel(const float* __restrict__ out, const long long* __restrict__ ys, const float* __restrict__ mult,
+                      int use_log1p, float* __restrict__ grad_out, float* __restrict__ row_loss,
+                      float* __restrict__ row_gmult, float* __restrict__ row_correct, int B, int K, float grad_scale) {
+    __shared__ float s_f[4];
+    __shared__ ValIdx s_vi[4];
+    const int i = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const float* o = out + static_cast<size_t>(i) * K;
+    const int y = static_cast<int>(ys[i % B]);
+    const float m = use_log1p ? mult[0] : 1.f;
+    auto value = [&](float x) { return use_log1p ? log1pf(powf(x, m)) : x; };
+
+    float vmax = -INFINITY;
+    ValIdx best{-INFINITY, 0x7fffffff};
+    for (int k = tid; k < K; k += 128) {
+        const float x = o[k];
+        vmax = fmaxf(vmax, value(x));
+        best = better(best, ValIdx{x, k});
+    }
+    vmax = warp_max(vmax);
+    best = warp_argmax(best);
+    if (lane == 0) {
+        s_f[warp] = vmax;
+        s_vi[warp] = best;
+    }
+    __syncthreads();
+    vmax = fmaxf(fmaxf(s_f[0], s_f[1]), fmaxf(s_f[2], s_f[3]));
+    best = better(better(s_vi[0], s_vi[1]), better(s_vi[2], s_vi[3]));
+    __syncthreads();
+
+    float se = 0.f;
+    for (int k = tid; k < K; k += 128) se += expf(value(o[k]) - vmax);
+    se = warp_sum(se);
+    if (lane == 0) s_f[warp] = se;
+    __syncthreads();
+    se = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
+    const float lse = vmax + logf(se);
+    __syncthreads();
+
+    float gm = 0.f;
+    if (grad_out != nullptr) {
+        float* g = grad_out + static_cast<size_t>(i) * K;
+        for (int k = tid; k < K; k += 128) {
+            const float x = o[k];
+            const float gv = (expf(value(x) - lse) - (k == y ? 1.f : 0.f)) * grad_scale;
+            if (use_log1p) {
+                // d log1p(x^m) / dx = m x^(m-1) / (1 + x^m); d / dm = x^m log(x) / (1 + x^m), 0 at x == 0 (torch's pow
+                // backward: zero where the base is 0 and the exponent >= 0)
+                const float pw = powf(x, m);
+                const float q = gv / (1.f + pw);
+                g[k] = m == 0.f ? 0.f : q * (m * powf(x, m - 1.f));
+                gm += (x == 0.f && m >= 0.f) ? 0.f : q * (pw * logf(x));
+            } else {
+                g[k] = gv;
+            }
+        }
+    }
+    gm = warp_sum(gm);
+    if (lane == 0) s_f[warp] = gm;
+    __syncthreads();
+    if (tid == 0) {
+        row_loss[i] = (y >= 0 && y < K) ? lse - value(o[y]) : 0.f;
+        row_gmult[i] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
+        row_correct[i] = best.i == y ? 1.f : 0.f;
+    }
+}
+
+// ---- finalize -------------------------------------------------------------------------------------------------------
+// One CTA of 256 threads: fixed-order sums of the partial arrays, then train.py:212-229's weighting.
+// result[0] align, [1] tanh, [2] class, [3] loss, [4] number of correct predictions, [5] d loss / d multiplier, [6..7] 0.
+__device__ __forceinline__ float block_sum_256(const float* __restrict__ v, int n, float* s_red) {
+    float a = 0.f;
+    for (int i = threadIdx.x; i < n; i += 256) a += v[i];
+    a = warp_sum(a);
+    __syncthreads();  // s_red may still be read from the previous call
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = a;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_red[w];
+    return t;
+}
+
+__global__ void __launch_bounds__(256)
+    loss_finalize_kernel(const float* __restrict__ align_partial, int n_align, const float* __restrict__ tanh_partial,
+                         int n_tanh_per_view, const float* __restrict__ row_loss, const float* __restrict__ row_gmult,
+                         const float* __restrict__ row_correct, int rows, float n_patches, float n_protos,
+                         float align_w, float tanh_w, float class_w, int pretrain, int finetune,
+                         float* __restrict__ result) {
+    __shared__ float s_red[8];
+    const float a = block_sum_256(align_partial, n_align, s_red) / n_patches;
+    const float t1 = block_sum_256(tanh_partial, n_tanh_per_view, s_red) / n_protos;
+    const float t2 = block_sum_256(tanh_partial + n_tanh_per_view, n_tanh_per_view, s_red) / n_protos;
+    float cl = 0.f, gm = 0.f, correct = 0.f;
+    if (!pretrain) {
+        cl = block_sum_256(row_loss, rows, s_red) / static_cast<float>(rows);
+        gm = block_sum_256(row_gmult, rows, s_red);
+        correct = block_sum_256(row_correct, rows, s_red);
+    }
+    if (threadIdx.x == 0) {
+        const float th = -(t1 + t2) / 2.f;
+        float loss = 0.f;
+        if (!finetune) loss = align_w * a + tanh_w * th;
+        if (!pretrain) loss = finetune ? class_w * cl : loss + class_w * cl;
+        result[0] = a;
+        result[1] = th;
+        result[2] = cl;
+        result[3] = loss;
+        result[4] = correct;
+        result[5] = gm;
+        result[6] = 0.f;
+        result[7] = 0.f;
+    }
+}
+
+// buf *= *scale unless *scale == 1 (the usual loss.backward() case costs one tiny launch and no pass over memory).
+__global__ void scale_unless_one_kernel(float* __restrict__ buf, long long n, const float* __restrict__ scale) {
+    const float s = scale[0];
+    if (s == 1.f) return;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) buf[i] *= s;
+}
+
+// ---- softmax over prototypes + spatial pooling on an NCHW map, forward ------------------------------------------------
+// z [N, P, HW] -> pf [N, P, HW] = softmax over P per position; per-CTA pooling partials over its 32 positions:
+// part_val [N, tiles, P] (max or sum), part_idx [N, tiles, P] (position of the maximum, lowest on ties; max mode only).
+// grid = (tiles = ceil(HW / 32), N), block = (32, 32).
+__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+    softmax_pool_nchw_kernel(const float* __restrict__ z, float* __restrict__ pf, float* __restrict__ part_val,
+                             int* __restrict__ part_idx, int mode_sum, int P, int HW) {
+    __shared__ float s_red[TRAIN_TY][TRAIN_TX + 1];
+    __shared__ float s_col[TRAIN_TX];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int n = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
+    const bool ok = hw < HW;
+    const size_t base = static_cast<size_t>(n) * P * HW + hw;
+    const float* zp = z + base;
+
+    float m = -INFINITY;
+    if (ok)
+        for (int c = ty; c < P; c += TRAIN_TY) m = fmaxf(m, zp[static_cast<size_t>(c) * HW]);
+    s_red[ty][tx] = m;
+    __syncthreads();
+    if (ty == 0) {
+        float mm = -INFINITY;
+        for (int j = 0; j < TRAIN_TY; ++j) mm = fmaxf(mm, s_red[j][tx]);
+        s_col[tx] = mm;
+    }
+    __syncthreads();
+    m = s_col[tx];
+
+    float s = 0.f;
+    if (ok)
+        for (int c = ty; c < P; c += TRAIN_TY) s += expf(zp[static_cast<size_t>(c) * HW] - m);
+    __syncthreads();  // s_col (the maxima) has been read by everyone
+    s_red[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0) s_col[tx] = column_sum(s_red, tx);
+    __syncthreads();
+    s = s_col[tx];
+
+    float* op = pf + base;
+    float* pv = part_val + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
+    int* pi = part_idx == nullptr ? nullptr : part_idx + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
+    for (int c = ty; c < P; c += TRAIN_TY) {  // warp-uniform trip count: every lane takes part in the shuffles
+        float y = 0.f;
+        if (ok) {
+            y = expf(zp[static_cast<size_t>(c) * HW] - m) / s;
+            op[static_cast<size_t>(c) * HW] = y;
+        }
+        if (mode_sum) {
+            const float t = warp_sum(y);
+            if (tx == 0) pv[c] = t;
+        } else {
+            const ValIdx best = warp_argmax(ValIdx{ok ? y : -1.f, hw});
+            if (tx == 0) {
+                pv[c] = best.v;
+                pi[c] = best.i;
+            }
+        }
+    }
+}
+
+// pooled [N, P] (and argmax [N, P] in max mode) from the per-tile partials, in tile order.
+// grid = (ceil(P / 128), N), block = 128.
+__global__ void __launch_bounds__(128)
+    pool_fold_nchw_kernel(const float* __restrict__ part_val, const int* __restrict__ part_idx, int mode_sum,
+                          float* __restrict__ pooled, int* __restrict__ argmax, int P, int tiles) {
+    const int n = blockIdx.y, p = blockIdx.x * 128 + threadIdx.x;
+    if (p >= P) return;
+    const size_t base = static_cast<size_t>(n) * tiles * P + p;
+    if (mode_sum) {
+        float a = 0.f;
+        for (int t = 0; t < tiles; ++t) a += part_val[base + static_cast<size_t>(t) * P];
+        pooled[static_cast<size_t>(n) * P + p] = a;
+    } else {
+        ValIdx best{part_val[base], part_idx[base]};
+        for (int t = 1; t < tiles; ++t)
+            best = better(best, ValIdx{part_val[base + static_cast<size_t>(t) * P], part_idx[base + static_cast<size_t>(t) * P]});
+        pooled[static_cast<size_t>(n) * P + p] = best.v;
+        argmax[static_cast<size_t>(n) * P + p] = best.i;
+    }
+}
+
+// ---- backward ---------------------------------------------------------------------------------------------------------
+// g[c] = grad_pf[n, c, hw] (0 if grad_pf == nullptr) + grad_pooled[n, c] * (sum mode ? 1 : hw == argmax[n, c]);
+// grad_z = pf * (g - sum_c g * pf)   (softmax backward of the sum of both incoming gradients).
+// grid = (ceil(HW / 32), N), block = (32, 32).
+__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+    softmax_pool_nchw_bwd_kernel(const float* __restrict__ pf, const float* __restrict__ grad_pf,
+                                 const float* __restrict__ grad_pooled, const int* __restrict__ argmax, int mode_sum,
+                                 float* __restrict__ grad_z, int P, int HW) {
+    __shared__ float s_dot[TRAIN_TY][TRAIN_TX + 1];
+    __shared__ float s_col[TRAIN_TX];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int n = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
+    const bool ok = hw < HW;
+    const size_t base = static_cast<size_t>(n) * P * HW + hw;
+    const float* yp = pf + base;
+    const float* gp = grad_pf == nullptr ? nullptr : grad_pf + base;
+    const float* gpool = grad_pooled == nullptr ? nullptr : grad_pooled + static_cast<size_t>(n) * P;
+    const int* am = argmax == nullptr ? nullptr : argmax + static_cast<size_t>(n) * P;
+    auto incoming = [&](int c) {
+        float g = gp == nullptr ? 0.f : gp[static_cast<size_t>(c) * HW];
+        if (gpool != nullptr && (mode_sum || am[c] == hw)) g += gpool[c];
+        return g;
+    };
+    float acc = 0.f;
+    if (ok)
+        for (int c = ty; c < P; c += TRAIN_TY) acc = fmaf(incoming(c), yp[static_cast<size_t>(c) * HW], acc);
+    s_dot[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0) s_col[tx] = column_sum(s_dot, tx);
+    __syncthreads();
+    if (!ok) return;
+    const float dot = s_col[tx];
+    float* out = grad_z + base;
+    for (int c = ty; c < P; c += TRAIN_TY)
+        __stcs(out + static_cast<size_t>(c) * HW, yp[static_cast<size_t>(c) * HW] * (incoming(c) - dot));
+}
+
+}  // namespace cpn

@@ -33,6 +33,8 @@ DEFAULT_PRECISION = os.environ.get("CPN_PRECISION", "fp32")
 USE_PLANS = os.environ.get("CPN_NO_PLAN", "0") != "1"
 # Replay a recorded plan as one CUDA graph from its second run on (small batches are launch-bound otherwise).
 USE_GRAPHS = os.environ.get("CPN_GRAPHS", "1") != "0"
+# Under autograd on a CUDA tensor, run softmax + pooling of the head (forward and backward) in the training kernels.
+TRAIN_KERNELS = os.environ.get("CPN_TRAIN_KERNELS", "1") != "0"
 MAX_PLANS = 8  # recorded plans kept per (module, device), least recently used dropped first
 
 _LOCK = threading.RLock()
@@ -58,6 +60,29 @@ def use_fused(module: nn.Module, x: torch.Tensor) -> bool:
         raise _lib.CpnError(
             "count_pipnet_b200 runs its inference forward on a B200 only (input is on %s); there is no CPU fallback. "
             "Move the module and input to CUDA, or enable autograd to use the composed PyTorch modules." % x.device)
+    return True
+
+
+def use_train_head(module: nn.Module, features: torch.Tensor, want_max: bool) -> bool:
+    """True when the autograd (composed) forward should hand its head to the training kernels of pipnet/train.py:
+    a CUDA fp32 map, the add-on ending in nn.Softmax(dim=1) (not the Gumbel variant, whose noise draw and
+    straight-through estimator stay torch ops), and for PIP-Net the stock AdaptiveMaxPool2d((1, 1)) + Flatten pool.
+    CPN_TRAIN_KERNELS=0 keeps the torch modules (A/B)."""
+    if not TRAIN_KERNELS or not features.is_cuda or features.dtype != torch.float32 or features.dim() != 4:
+        return False
+    add_on = getattr(module, "_add_on", None)
+    if not isinstance(add_on, nn.Sequential) or len(add_on) == 0:
+        return False
+    last = add_on[len(add_on) - 1]
+    if type(last) is not nn.Softmax or last.dim != 1:
+        return False
+    if want_max:
+        pool = getattr(module, "_pool", None)
+        if not isinstance(pool, nn.Sequential) or len(pool) != 2:
+            return False
+        if type(pool[0]) is not nn.AdaptiveMaxPool2d or pool[0].output_size not in (1, (1, 1)) \
+                or pool[0].return_indices or type(pool[1]) is not nn.Flatten:
+            return False
     return True
 
 

@@ -265,3 +265,42 @@ def topk_update(pooled, argmax, image_base, top_val, top_img, top_tok, top_cnt, 
     B, P = pooled.shape
     _lib.call("cpn_topk_update", _ph(plan), ptr(pooled), ptr(argmax), B, P, top_val.shape[0], int(image_base),
               ptr(top_val), ptr(top_img), ptr(top_tok), ptr(top_cnt), _stream())
+
+
+# ---- training side of the head (no plans) --------------------------------------------------------------------------
+def pipnet_loss_ws_floats(B, P, HW) -> int:
+    return int(_lib.load().cpn_pipnet_loss_ws_floats(B, P, HW))
+
+
+def pipnet_loss(pf, pooled, out, ys, norm_mult, B, P, HW, K, align_w, tanh_w, class_w, tanh_coeff, eps_tanh, pretrain,
+                finetune, use_log1p, grad_pf, grad_pooled, grad_out, result, workspace):
+    """Loss values and gradients of pipnet/train.py's calculate_loss: see cpn_pipnet_loss in include/cpn_b200.h."""
+    _need_cuda(pf, pooled, out, ys, norm_mult, grad_pf, grad_pooled, grad_out, result, workspace)
+    _lib.call("cpn_pipnet_loss", ptr(pf), ptr(pooled), ptr(out), ptr(ys), ptr(norm_mult), B, P, HW, K, float(align_w),
+              float(tanh_w), float(class_w), float(tanh_coeff), float(eps_tanh), int(bool(pretrain)),
+              int(bool(finetune)), int(bool(use_log1p)), ptr(grad_pf), ptr(grad_pooled), ptr(grad_out), ptr(result),
+              ptr(workspace), _stream())
+
+
+def scale_unless_one(buf, scale):
+    _need_cuda(buf, scale)
+    _lib.call("cpn_scale_unless_one", ptr(buf), buf.numel(), ptr(scale), _stream())
+
+
+def softmax_pool_nchw_ws_floats(N, P, HW) -> int:
+    return int(_lib.load().cpn_softmax_pool_nchw_ws_floats(N, P, HW))
+
+
+def softmax_pool_nchw(z, mode, pf, pooled, argmax, workspace):
+    """z [N, P, H, W] -> pf (softmax over P), pooled [N, P] (max with argmax, or sum): cpn_softmax_pool_nchw."""
+    _need_cuda(z, pf, pooled, argmax, workspace)
+    N, P = z.shape[0], z.shape[1]
+    _lib.call("cpn_softmax_pool_nchw", ptr(z), mode, ptr(pf), ptr(pooled), ptr(argmax), N, P, z[0, 0].numel(),
+              ptr(workspace), _stream())
+
+
+def softmax_pool_nchw_bwd(pf, grad_pf, grad_pooled, argmax, mode, grad_z):
+    _need_cuda(pf, grad_pf, grad_pooled, argmax, grad_z)
+    N, P = pf.shape[0], pf.shape[1]
+    _lib.call("cpn_softmax_pool_nchw_bwd", ptr(pf), ptr(grad_pf), ptr(grad_pooled), ptr(argmax), mode, ptr(grad_z), N, P,
+              pf[0, 0].numel(), _stream())

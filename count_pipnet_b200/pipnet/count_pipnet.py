@@ -51,8 +51,16 @@ class CountPIPNet(nn.Module):
         if engine.use_fused(self, xs):
             return engine.network_forward(self, xs, inference)
         features = self._net(xs)
-        proto_features = self._add_on(features)
-        counts = self._calculate_counts_for_testing(proto_features)
+        if engine.use_train_head(self, features, want_max=False):
+            # autograd forward on a B200 with the plain-softmax activation: softmax + spatial sum as one kernel
+            from .train import softmax_pool_head
+            z = features
+            for layer in list(self._add_on)[:-1]:
+                z = layer(z)
+            proto_features, counts = softmax_pool_head(z, "sum")
+        else:
+            proto_features = self._add_on(features)
+            counts = self._calculate_counts_for_testing(proto_features)
         if self._use_ste:
             rounded = self.ste_round(counts)
             clamped = self.ste_clamp(rounded, 0, self._max_count, self._is_clamp_backward_identity)

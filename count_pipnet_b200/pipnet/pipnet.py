@@ -43,8 +43,16 @@ class PIPNet(nn.Module):
         if engine.use_fused(self, xs):
             return engine.network_forward(self, xs, inference)
         features = self._net(xs)
-        proto_features = self._add_on(features)
-        pooled = self._pool(proto_features)
+        if engine.use_train_head(self, features, want_max=True):
+            # autograd forward on a B200: softmax + max pool (and their backward) as one kernel each
+            from .train import softmax_pool_head
+            z = features
+            for layer in list(self._add_on)[:-1]:  # the optional 1x1 add-on conv stays a torch module
+                z = layer(z)
+            proto_features, pooled = softmax_pool_head(z, "max")
+        else:
+            proto_features = self._add_on(features)
+            pooled = self._pool(proto_features)
         if inference:
             # prototypes with similarity below 0.1 are ignored at inference (pipnet/pipnet.py:36)
             pooled = torch.where(pooled < 0.1, 0., pooled)

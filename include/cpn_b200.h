@@ -260,6 +260,42 @@ long long cpn_preprocess_ws_ints(int Hs, int Ws, int Ho, int Wo);
 int cpn_preprocess_u8(cpn_plan* plan, const unsigned char* src, float* out, int* ws, int B, int Hs, int Ws, int Ho, int Wo,
                       const float* mean3, const float* std3, void* stream);
 
+/* ---- training side of the prototype head ----------------------------------------------- */
+/* These four take the map as the reference's modules return it: [N, P, H*W] fp32, NCHW. No plans: a training step is
+ * not replayed. All reductions run in a fixed order (two runs give the same bits).
+ *
+ * calculate_loss + align_loss (pipnet/train.py:165-243, 253-265) and every gradient of the loss in one call:
+ *   align = -mean_n log(sum_c pf1[n,c] pf2[n,c] + 1e-12)         (train.py:173, both directions have this value)
+ *   tanh  = -(mean_p log(tanh(sum_b coeff*pooled1[b,p]) + eps) + the same for pooled2) / 2          (train.py:198-201)
+ *   class = NLLLoss(mean)(log_softmax(use_log1p ? log1p(out^m) : out), cat(ys, ys))               (train.py:216-222)
+ *   loss  = finetune ? class_w*class : align_w*align + tanh_w*tanh (+ class_w*class unless pretrain) (train.py:212-229)
+ * proto_features [2B, P, HW], pooled [2B, P], out [2B, K] (view 1 = rows [0, B), view 2 = rows [B, 2B): the halves of
+ * train.py:167-168's chunk(2)), ys [B] int64 labels in [0, K), norm_mult = the classifier's normalization_multiplier (one
+ * device float). out / ys / norm_mult are ignored when pretrain != 0. Outputs: grad_pf / grad_pooled / grad_out = d loss
+ * / d input (same shapes; any may be NULL; grad_pf and grad_pooled must be NULL when finetune != 0, the loss does not
+ * depend on them); result [8] = {align, tanh, class, loss, number of rows whose arg-max(out) is the label
+ * (train.py:233-235), d loss / d norm_mult, 0, 0}; workspace: cpn_pipnet_loss_ws_floats(B, P, HW) floats. */
+long long cpn_pipnet_loss_ws_floats(int B, int P, int HW);
+int cpn_pipnet_loss(const float* proto_features, const float* pooled, const float* out, const long long* ys,
+                    const float* norm_mult, int B, int P, int HW, int K, float align_w, float tanh_w, float class_w,
+                    float tanh_coeff, float eps_tanh, int pretrain, int finetune, int use_log1p, float* grad_pf,
+                    float* grad_pooled, float* grad_out, float* result, float* workspace, void* stream);
+/* buf[0..n) *= *scale unless *scale == 1 (scale: one device float). The backward of cpn_pipnet_loss's autograd node:
+ * loss.backward() (train.py:103) arrives with 1, and then no pass over the gradients is spent. */
+int cpn_scale_unless_one(float* buf, long long n, const float* scale, void* stream);
+/* Softmax(dim=1) over the prototypes of an NCHW map and the spatial pooling of the autograd (training) forward:
+ * pipnet/pipnet.py:32-33 with :96 and :105-108 (mode CPN_POOL_MAX; argmax [N, P] int32 = flattened position of the
+ * maximum, the first one on ties as AdaptiveMaxPool2d's backward picks it), pipnet/count_pipnet.py:356-360 and :88
+ * (mode CPN_POOL_SUM; argmax unused, may be NULL). z -> proto_features [N, P, HW], pooled [N, P];
+ * workspace: cpn_softmax_pool_nchw_ws_floats(N, P, HW) floats. */
+long long cpn_softmax_pool_nchw_ws_floats(int N, int P, int HW);
+int cpn_softmax_pool_nchw(const float* z, int mode, float* proto_features, float* pooled, int* argmax, int N, int P,
+                          int HW, float* workspace, void* stream);
+/* Its backward (what autograd does for those modules, as one kernel): grad_z = pf * (g - sum_c g*pf) with
+ * g = grad_pf (NULL = zeros) + grad_pooled (NULL = zeros) routed to the arg-max position (max) or to every position (sum). */
+int cpn_softmax_pool_nchw_bwd(const float* proto_features, const float* grad_pf, const float* grad_pooled,
+                              const int* argmax, int mode, float* grad_z, int N, int P, int HW, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

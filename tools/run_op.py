@@ -97,6 +97,35 @@ def main():
         fn = lambda: ops.mlp_fused(y, w1g, w2, a.M, C, stats, colsum, b1, b2, scale, x)
         nbytes = y.numel() * 2 + x.numel() * 8 + w1g.numel() * 4
         flops = 16.0 * a.M * C * C
+    elif a.op in ("pipnet_loss", "head_fwd", "head_bwd"):
+        # training side of the head: --B image PAIRS, --C prototypes, --H x --W map, --N classes
+        z = (torch.randn(2 * a.B, a.C, a.H, a.W, generator=g) * 3).to(dev)
+        pf = torch.softmax(z, dim=1)
+        pooled = pf.amax(dim=(2, 3))
+        K = min(a.N, 1000)
+        out = pooled @ torch.relu(torch.randn(K, a.C, generator=g)).to(dev).t()
+        ys = torch.randint(0, K, (a.B,), generator=g).to(dev)
+        mult = torch.tensor([1.3], device=dev)
+        gpf, gpl, go = torch.empty_like(pf), torch.empty_like(pooled), torch.empty_like(out)
+        flops = 0.0
+        if a.op == "pipnet_loss":
+            res = torch.empty(8, device=dev)
+            ws = torch.empty(ops.pipnet_loss_ws_floats(a.B, a.C, a.H * a.W), device=dev)
+            fn = lambda: ops.pipnet_loss(pf, pooled, out, ys, mult, a.B, a.C, a.H * a.W, K, 5., 2., 2., 1., 1e-8, False,
+                                         False, True, gpf, gpl, go, res, ws)
+            nbytes = 8 * pf.numel()
+        else:
+            arg = torch.empty(2 * a.B, a.C, device=dev, dtype=torch.int32)
+            ws = torch.empty(ops.softmax_pool_nchw_ws_floats(2 * a.B, a.C, a.H * a.W), device=dev)
+            if a.op == "head_fwd":
+                fn = lambda: ops.softmax_pool_nchw(z, _lib.POOL_MAX, pf, pooled, arg, ws)
+                nbytes = 8 * pf.numel()
+            else:
+                ops.softmax_pool_nchw(z, _lib.POOL_MAX, pf, pooled, arg, ws)
+                gpf.normal_()
+                gpl.normal_()
+                fn = lambda: ops.softmax_pool_nchw_bwd(pf, gpf, gpl, arg, _lib.POOL_MAX, z)
+                nbytes = 12 * pf.numel()
     else:
         raise SystemExit("unknown op")
     for _ in range(2):
