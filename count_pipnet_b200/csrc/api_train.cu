@@ -5,11 +5,32 @@
 #include "api_common.h"
 #include "train_kernels.cuh"
 
+#include <cstdint>
+#include <initializer_list>
+
 using namespace cpn_api;
 
 namespace {
 
-inline int tiles_of(int HW) { return (HW + cpn::TRAIN_TX - 1) / cpn::TRAIN_TX; }
+inline int tiles_of(int HW) { return (HW + cpn::TRAIN_TILE - 1) / cpn::TRAIN_TILE; }
+
+// The map kernels read 4 neighbouring positions per lane when rows and bases allow 16-byte accesses.
+inline bool aligned16(const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+inline int vec_of(int HW, std::initializer_list<const void*> maps) {
+    if (HW % 4 != 0) return 1;
+    for (const void* p : maps)
+        if (!aligned16(p)) return 1;
+    return 4;
+}
+// Threads per CTA: (32 / vec) lanes per channel row x as many channel groups as there are channels, at most 512 threads,
+// a whole number of warps.
+inline int threads_of(int vec, int P) {
+    const int L = 32 / vec, cg_max = cpn::TRAIN_THREADS / L;
+    int cg = P < cg_max ? P : cg_max;
+    int threads = L * cg;
+    threads = (threads + 31) / 32 * 32;
+    return threads;
+}
 inline int tanh_blocks(int P) { return (P + 127) / 128; }
 
 struct LossWs {  // layout of the caller's workspace, in floats
@@ -56,9 +77,14 @@ extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     set_info("pipnet_loss", 4.0 * B * P * HW, (grad_pf ? 16.0 : 8.0) * B * P * HW);
 
-    cpn::align_loss_kernel<<<dim3(tiles, B), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0, st>>>(
-        proto_features, grad_pf, workspace + w.align, B, P, HW, align_eps,
-        static_cast<float>(-0.5 * align_w / n_patches));
+    const int vec = vec_of(HW, {proto_features, grad_pf});
+    const float align_scale = static_cast<float>(-0.5 * align_w / n_patches);
+    if (vec == 4)
+        cpn::align_loss_kernel<4><<<dim3(tiles, B), threads_of(4, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
+                                                                               B, P, HW, align_eps, align_scale);
+    else
+        cpn::align_loss_kernel<1><<<dim3(tiles, B), threads_of(1, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
+                                                                               B, P, HW, align_eps, align_scale);
     CPN_CUDA(cudaGetLastError());
     cpn::tanh_loss_kernel<<<dim3(tanh_blocks(P), 2), 128, 0, st>>>(pooled, grad_pooled, workspace + w.tanh, B, P,
                                                                     tanh_coeff, eps_tanh,
@@ -107,8 +133,13 @@ extern "C" int cpn_softmax_pool_nchw(const float* z, int mode, float* proto_feat
     int* part_idx = reinterpret_cast<int*>(workspace + static_cast<size_t>(N) * tiles * P);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     set_info("softmax_pool_nchw", 0.0, 8.0 * N * P * HW);
-    cpn::softmax_pool_nchw_kernel<<<dim3(tiles, N), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0, st>>>(
-        z, proto_features, part_val, mode == CPN_POOL_MAX ? part_idx : nullptr, mode == CPN_POOL_SUM, P, HW);
+    int* idx = mode == CPN_POOL_MAX ? part_idx : nullptr;
+    if (vec_of(HW, {z, proto_features}) == 4)
+        cpn::softmax_pool_nchw_kernel<4><<<dim3(tiles, N), threads_of(4, P), 0, st>>>(z, proto_features, part_val, idx,
+                                                                                      mode == CPN_POOL_SUM, P, HW);
+    else
+        cpn::softmax_pool_nchw_kernel<1><<<dim3(tiles, N), threads_of(1, P), 0, st>>>(z, proto_features, part_val, idx,
+                                                                                      mode == CPN_POOL_SUM, P, HW);
     CPN_CUDA(cudaGetLastError());
     cpn::pool_fold_nchw_kernel<<<dim3((P + 127) / 128, N), 128, 0, st>>>(part_val, part_idx, mode == CPN_POOL_SUM, pooled,
                                                                         argmax, P, tiles);
@@ -125,9 +156,13 @@ extern "C" int cpn_softmax_pool_nchw_bwd(const float* proto_features, const floa
         return fail("cpn_softmax_pool_nchw_bwd: max pooling needs the forward's argmax");
     if (N <= 0 || N > 65535 || P <= 0 || HW <= 0) return fail("cpn_softmax_pool_nchw_bwd: bad N=%d P=%d HW=%d", N, P, HW);
     set_info("softmax_pool_nchw_bwd", 0.0, (grad_pf ? 12.0 : 8.0) * N * P * HW);
-    cpn::softmax_pool_nchw_bwd_kernel<<<dim3(tiles_of(HW), N), dim3(cpn::TRAIN_TX, cpn::TRAIN_TY), 0,
-                                        static_cast<cudaStream_t>(stream)>>>(proto_features, grad_pf, grad_pooled, argmax,
-                                                                             mode == CPN_POOL_SUM, grad_z, P, HW);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (vec_of(HW, {proto_features, grad_pf, grad_z}) == 4)
+        cpn::softmax_pool_nchw_bwd_kernel<4><<<dim3(tiles_of(HW), N), threads_of(4, P), 0, st>>>(
+            proto_features, grad_pf, grad_pooled, argmax, mode == CPN_POOL_SUM, grad_z, P, HW);
+    else
+        cpn::softmax_pool_nchw_bwd_kernel<1><<<dim3(tiles_of(HW), N), threads_of(1, P), 0, st>>>(
+            proto_features, grad_pf, grad_pooled, argmax, mode == CPN_POOL_SUM, grad_z, P, HW);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }

@@ -20,82 +20,159 @@
 
 namespace cpn {
 
-constexpr int TRAIN_TX = 32;  // spatial positions per CTA (one coalesced 128-byte row segment per channel)
-constexpr int TRAIN_TY = 32;  // channel groups per CTA: 1024 threads, two CTAs per SM, so that the second pass of a
-                              // CTA (32 positions x P channels x 2 tensors) is still in L2 when it is read again
+constexpr int TRAIN_TILE = 32;      // spatial positions per CTA: one 128-byte row segment per channel
+constexpr int TRAIN_THREADS = 512;  // at most; two CTAs per SM, so that one CTA's reduction phases overlap the other's loads
+                                    // and the second pass of a CTA (32 positions x P channels) is still in L2
 
-// Sum over the TY partials of one spatial position in a fixed order (ty = 0 .. TY-1).
-__device__ __forceinline__ float column_sum(const float (*s)[TRAIN_TX + 1], int tx) {
-    float d = 0.f;
-#pragma unroll 8
-    for (int j = 0; j < TRAIN_TY; ++j) d += s[j][tx];
-    return d;
+// VEC = 4 when H*W % 4 == 0 and the maps are 16-byte aligned: a lane owns 4 neighbouring positions (one LDG.128 per
+// channel), 8 lanes cover the tile and a warp reads four channel rows per instruction. VEC = 1 otherwise (lane = position).
+template <int VEC>
+__device__ __forceinline__ void ldv(const float* __restrict__ p, float (&o)[VEC]) {
+    if constexpr (VEC == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        o[0] = t.x, o[1] = t.y, o[2] = t.z, o[3] = t.w;
+    } else {
+        o[0] = *p;
+    }
+}
+template <int VEC>
+__device__ __forceinline__ void stv_cs(float* __restrict__ p, const float (&o)[VEC]) {  // streaming store
+    if constexpr (VEC == 4) {
+        __stcs(reinterpret_cast<float4*>(p), make_float4(o[0], o[1], o[2], o[3]));
+    } else {
+        __stcs(p, o[0]);
+    }
+}
+template <int VEC>
+__device__ __forceinline__ void stv(float* __restrict__ p, const float (&o)[VEC]) {
+    if constexpr (VEC == 4) {
+        *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]);
+    } else {
+        *p = o[0];
+    }
+}
+
+// Reduction over the channel groups of a CTA for each of the tile's 32 positions, in a fixed order: lanes of a warp that
+// share positions (butterfly), then the warps in index order. Every thread passes its VEC partials for positions
+// hwl * VEC + k; afterwards s_col[0..32) holds the totals (read them before the next call).
+template <int VEC, bool MAX>
+__device__ __forceinline__ void tile_reduce(float (&acc)[VEC], float (*s_red)[TRAIN_TILE + 1], float* s_col) {
+    constexpr int L = 32 / VEC;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+#pragma unroll
+    for (int o = L; o < 32; o <<= 1) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const float other = __shfl_xor_sync(0xffffffffu, acc[k], o);
+            acc[k] = MAX ? fmaxf(acc[k], other) : acc[k] + other;
+        }
+    }
+    if (lane < L) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) s_red[warp][lane * VEC + k] = acc[k];
+    }
+    __syncthreads();
+    if (tid < TRAIN_TILE) {
+        float r = s_red[0][tid];
+        for (int w = 1; w < nwarps; ++w) r = MAX ? fmaxf(r, s_red[w][tid]) : r + s_red[w][tid];
+        s_col[tid] = r;
+    }
+    __syncthreads();
 }
 
 // ---- align loss -----------------------------------------------------------------------------------------------------
 // pf [2B, P, HW]: view 1 = images [0, B), view 2 = images [B, 2B). For patch n = (b, hw): d_n = sum_c pf1 * pf2,
 // loss = -mean_n log(d_n + eps) (the two directions of train.py:173 have the same value); d loss / d pf1 = grad_scale *
 // pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
-// grid = (ceil(HW / 32), B), block = (32, 32). partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
-__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+// grid = (ceil(HW / 32), B), block = (32 / VEC) * channel groups. partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
     align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial, int B, int P,
                       int HW, float eps, float grad_scale) {
-    __shared__ float s_dot[TRAIN_TY][TRAIN_TX + 1];
-    __shared__ float s_coef[TRAIN_TX];
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int b = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
-    const bool ok = hw < HW;
+    constexpr int L = 32 / VEC;
+    constexpr int U = VEC == 4 ? 2 : 4;  // channels in flight per thread and view
+    __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
+    __shared__ float s_col[TRAIN_TILE];
+    const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
+    const int b = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
+    const bool ok = hw0 < HW;
     const size_t img = static_cast<size_t>(P) * HW;
-    const size_t off1 = static_cast<size_t>(b) * img + hw, off2 = off1 + static_cast<size_t>(B) * img;
+    const size_t off1 = static_cast<size_t>(b) * img + hw0, off2 = off1 + static_cast<size_t>(B) * img;
     const float* p1 = pf + off1;
     const float* p2 = pf + off2;
-    float acc = 0.f;
-    if (ok) {
-        int c = ty;
-        for (; c + 3 * TRAIN_TY < P; c += 4 * TRAIN_TY) {
-            float a[4], v[4];
+    float acc[VEC];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                a[j] = p1[static_cast<size_t>(c + j * TRAIN_TY) * HW];
-                v[j] = p2[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+    for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
+    if (ok) {
+        int c = cg;
+        for (; c + (U - 1) * CG < P; c += U * CG) {
+            float a[U][VEC], v[U][VEC];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+                ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc = fmaf(a[j], v[j], acc);
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[u][k], v[u][k], acc[k]);
         }
-        for (; c < P; c += TRAIN_TY) acc = fmaf(p1[static_cast<size_t>(c) * HW], p2[static_cast<size_t>(c) * HW], acc);
+        for (; c < P; c += CG) {
+            float a[VEC], v[VEC];
+            ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+            ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[k], v[k], acc[k]);
+        }
     }
-    s_dot[ty][tx] = acc;
-    __syncthreads();
-    if (ty == 0) {
-        const float d = column_sum(s_dot, tx) + eps;
-        s_coef[tx] = ok ? grad_scale / d : 0.f;
-        const float l = warp_sum(ok ? -logf(d) : 0.f);
-        if (tx == 0) partial[static_cast<size_t>(b) * gridDim.x + blockIdx.x] = l;
+    tile_reduce<VEC, false>(acc, s_red, s_col);
+    if (tid < TRAIN_TILE) {  // warp 0: lane = position of the tile
+        const bool valid = blockIdx.x * TRAIN_TILE + tid < HW;
+        const float d = s_col[tid] + eps;
+        s_col[tid] = valid ? grad_scale / d : 0.f;
+        const float l = warp_sum(valid ? -logf(d) : 0.f);
+        if (tid == 0) partial[static_cast<size_t>(b) * gridDim.x + blockIdx.x] = l;
     }
     if (grad == nullptr) return;
     __syncthreads();
     if (!ok) return;
-    const float k = s_coef[tx];
+    float kf[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) kf[k] = s_col[hwl * VEC + k];
     float* g1 = grad + off1;
     float* g2 = grad + off2;
-    int c = ty;
-    for (; c + 3 * TRAIN_TY < P; c += 4 * TRAIN_TY) {
-        float a[4], v[4];
+    int c = cg;
+    for (; c + (U - 1) * CG < P; c += U * CG) {
+        float a[U][VEC], v[U][VEC];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            a[j] = p1[static_cast<size_t>(c + j * TRAIN_TY) * HW];
-            v[j] = p2[static_cast<size_t>(c + j * TRAIN_TY) * HW];
+        for (int u = 0; u < U; ++u) {
+            ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+            ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            __stcs(g1 + static_cast<size_t>(c + j * TRAIN_TY) * HW, k * v[j]);
-            __stcs(g2 + static_cast<size_t>(c + j * TRAIN_TY) * HW, k * a[j]);
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) {
+                const float t = a[u][k];
+                a[u][k] = kf[k] * v[u][k];
+                v[u][k] = kf[k] * t;
+            }
+            stv_cs<VEC>(g1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+            stv_cs<VEC>(g2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
         }
     }
-    for (; c < P; c += TRAIN_TY) {
-        const float a = p1[static_cast<size_t>(c) * HW], v = p2[static_cast<size_t>(c) * HW];
-        __stcs(g1 + static_cast<size_t>(c) * HW, k * v);
-        __stcs(g2 + static_cast<size_t>(c) * HW, k * a);
+    for (; c < P; c += CG) {
+        float a[VEC], v[VEC];
+        ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+        ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const float t = a[k];
+            a[k] = kf[k] * v[k];
+            v[k] = kf[k] * t;
+        }
+        stv_cs<VEC>(g1 + static_cast<size_t>(c) * HW, a);
+        stv_cs<VEC>(g2 + static_cast<size_t>(c) * HW, v);
     }
 }
 
@@ -274,60 +351,112 @@ __global__ void scale_unless_one_kernel(float* __restrict__ buf, long long n, co
 }
 
 // ---- softmax over prototypes + spatial pooling on an NCHW map, forward ------------------------------------------------
+// exp(x) for x <= 0 as one FMUL + MUFU.EX2 (relative error < 1e-6 for the entries that matter, x > -10).
+__device__ __forceinline__ float exp_neg(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+    return y;
+}
+
 // z [N, P, HW] -> pf [N, P, HW] = softmax over P per position; per-CTA pooling partials over its 32 positions:
 // part_val [N, tiles, P] (max or sum), part_idx [N, tiles, P] (position of the maximum, lowest on ties; max mode only).
-// grid = (tiles = ceil(HW / 32), N), block = (32, 32).
-__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+// grid = (tiles = ceil(HW / 32), N), block = (32 / VEC) * channel groups.
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
     softmax_pool_nchw_kernel(const float* __restrict__ z, float* __restrict__ pf, float* __restrict__ part_val,
                              int* __restrict__ part_idx, int mode_sum, int P, int HW) {
-    __shared__ float s_red[TRAIN_TY][TRAIN_TX + 1];
-    __shared__ float s_col[TRAIN_TX];
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int n = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
-    const bool ok = hw < HW;
-    const size_t base = static_cast<size_t>(n) * P * HW + hw;
+    constexpr int L = 32 / VEC;
+    __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
+    __shared__ float s_col[TRAIN_TILE];
+    const int tid = threadIdx.x, lane = tid & 31, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
+    const int n = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
+    const bool ok = hw0 < HW;
+    const size_t base = static_cast<size_t>(n) * P * HW + hw0;
     const float* zp = z + base;
 
-    float m = -INFINITY;
-    if (ok)
-        for (int c = ty; c < P; c += TRAIN_TY) m = fmaxf(m, zp[static_cast<size_t>(c) * HW]);
-    s_red[ty][tx] = m;
-    __syncthreads();
-    if (ty == 0) {
-        float mm = -INFINITY;
-        for (int j = 0; j < TRAIN_TY; ++j) mm = fmaxf(mm, s_red[j][tx]);
-        s_col[tx] = mm;
+    float m[VEC], s[VEC], x[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) m[k] = -INFINITY;
+    if (ok) {
+        int c = cg;
+        for (; c + CG < P; c += 2 * CG) {
+            float x2[VEC];
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+            ldv<VEC>(zp + static_cast<size_t>(c + CG) * HW, x2);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], fmaxf(x[k], x2[k]));
+        }
+        if (c < P) {
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
+        }
     }
-    __syncthreads();
-    m = s_col[tx];
-
-    float s = 0.f;
-    if (ok)
-        for (int c = ty; c < P; c += TRAIN_TY) s += expf(zp[static_cast<size_t>(c) * HW] - m);
-    __syncthreads();  // s_col (the maxima) has been read by everyone
-    s_red[ty][tx] = s;
-    __syncthreads();
-    if (ty == 0) s_col[tx] = column_sum(s_red, tx);
-    __syncthreads();
-    s = s_col[tx];
+    tile_reduce<VEC, true>(m, s_red, s_col);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        m[k] = s_col[hwl * VEC + k];
+        s[k] = 0.f;
+    }
+    if (ok) {
+        int c = cg;
+        for (; c + CG < P; c += 2 * CG) {
+            float x2[VEC];
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+            ldv<VEC>(zp + static_cast<size_t>(c + CG) * HW, x2);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x[k] - m[k]);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x2[k] - m[k]);
+        }
+        if (c < P) {
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x[k] - m[k]);
+        }
+    }
+    tile_reduce<VEC, false>(s, s_red, s_col);
+    float inv[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) inv[k] = 1.0f / s_col[hwl * VEC + k];
 
     float* op = pf + base;
     float* pv = part_val + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
     int* pi = part_idx == nullptr ? nullptr : part_idx + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
-    for (int c = ty; c < P; c += TRAIN_TY) {  // warp-uniform trip count: every lane takes part in the shuffles
-        float y = 0.f;
+    // the L lanes that share a channel row reduce among themselves; they also share the loop's trip count
+    unsigned gmask = 0xffffffffu;
+    if constexpr (L < 32) gmask = ((1u << L) - 1u) << (lane & ~(L - 1));
+    for (int c = cg; c < P; c += CG) {
+        float y[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) y[k] = 0.f;
         if (ok) {
-            y = expf(zp[static_cast<size_t>(c) * HW] - m) / s;
-            op[static_cast<size_t>(c) * HW] = y;
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) y[k] = exp_neg(x[k] - m[k]) * inv[k];
+            stv<VEC>(op + static_cast<size_t>(c) * HW, y);
         }
         if (mode_sum) {
-            const float t = warp_sum(y);
-            if (tx == 0) pv[c] = t;
+            float t = y[0];
+#pragma unroll
+            for (int k = 1; k < VEC; ++k) t += y[k];
+#pragma unroll
+            for (int o = L / 2; o > 0; o >>= 1) t += __shfl_xor_sync(gmask, t, o);
+            if (hwl == 0) pv[c] = t;
         } else {
-            const ValIdx best = warp_argmax(ValIdx{ok ? y : -1.f, hw});
-            if (tx == 0) {
-                pv[c] = best.v;
-                pi[c] = best.i;
+            // probabilities are >= 0, so their bit patterns order like the values: one integer REDUX per channel row
+            float lm = y[0];
+#pragma unroll
+            for (int k = 1; k < VEC; ++k) lm = fmaxf(lm, y[k]);
+            const unsigned bits = __float_as_uint(lm);
+            const unsigned mx = __reduce_max_sync(gmask, bits);
+            const unsigned vote = __ballot_sync(gmask, ok && bits == mx);
+            if (lane == __ffs(vote) - 1) {  // first lane = lowest position among equal maxima
+                int kk = 0;
+#pragma unroll
+                for (int k = VEC - 1; k >= 0; --k) kk = (y[k] == lm) ? k : kk;
+                pv[c] = lm;
+                pi[c] = hw0 + kk;
             }
         }
     }
@@ -357,38 +486,94 @@ __global__ void __launch_bounds__(128)
 // ---- backward ---------------------------------------------------------------------------------------------------------
 // g[c] = grad_pf[n, c, hw] (0 if grad_pf == nullptr) + grad_pooled[n, c] * (sum mode ? 1 : hw == argmax[n, c]);
 // grad_z = pf * (g - sum_c g * pf)   (softmax backward of the sum of both incoming gradients).
-// grid = (ceil(HW / 32), N), block = (32, 32).
-__global__ void __launch_bounds__(TRAIN_TX* TRAIN_TY)
+// grid = (ceil(HW / 32), N), block = (32 / VEC) * channel groups.
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
     softmax_pool_nchw_bwd_kernel(const float* __restrict__ pf, const float* __restrict__ grad_pf,
                                  const float* __restrict__ grad_pooled, const int* __restrict__ argmax, int mode_sum,
                                  float* __restrict__ grad_z, int P, int HW) {
-    __shared__ float s_dot[TRAIN_TY][TRAIN_TX + 1];
-    __shared__ float s_col[TRAIN_TX];
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int n = blockIdx.y, hw = blockIdx.x * TRAIN_TX + tx;
-    const bool ok = hw < HW;
-    const size_t base = static_cast<size_t>(n) * P * HW + hw;
+    constexpr int L = 32 / VEC;
+    __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
+    __shared__ float s_col[TRAIN_TILE];
+    const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
+    const int n = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
+    const bool ok = hw0 < HW;
+    const size_t base = static_cast<size_t>(n) * P * HW + hw0;
     const float* yp = pf + base;
     const float* gp = grad_pf == nullptr ? nullptr : grad_pf + base;
     const float* gpool = grad_pooled == nullptr ? nullptr : grad_pooled + static_cast<size_t>(n) * P;
-    const int* am = argmax == nullptr ? nullptr : argmax + static_cast<size_t>(n) * P;
-    auto incoming = [&](int c) {
-        float g = gp == nullptr ? 0.f : gp[static_cast<size_t>(c) * HW];
-        if (gpool != nullptr && (mode_sum || am[c] == hw)) g += gpool[c];
-        return g;
+    const int* am = (argmax == nullptr || mode_sum) ? nullptr : argmax + static_cast<size_t>(n) * P;
+    auto incoming = [&](int c, float (&g)[VEC]) {
+        if (gp != nullptr) {
+            ldv<VEC>(gp + static_cast<size_t>(c) * HW, g);
+        } else {
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) g[k] = 0.f;
+        }
+        if (gpool != nullptr) {
+            const float t = __ldg(gpool + c);
+            if (mode_sum) {
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) g[k] += t;
+            } else {
+                const int a = __ldg(am + c) - hw0;
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) g[k] += (a == k) ? t : 0.f;
+            }
+        }
     };
-    float acc = 0.f;
-    if (ok)
-        for (int c = ty; c < P; c += TRAIN_TY) acc = fmaf(incoming(c), yp[static_cast<size_t>(c) * HW], acc);
-    s_dot[ty][tx] = acc;
-    __syncthreads();
-    if (ty == 0) s_col[tx] = column_sum(s_dot, tx);
-    __syncthreads();
+    float acc[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
+    if (ok) {
+        int c = cg;
+        for (; c + CG < P; c += 2 * CG) {
+            float y0[VEC], y1[VEC], g0[VEC], g1[VEC];
+            ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+            ldv<VEC>(yp + static_cast<size_t>(c + CG) * HW, y1);
+            incoming(c, g0);
+            incoming(c + CG, g1);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(g0[k], y0[k], acc[k]);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(g1[k], y1[k], acc[k]);
+        }
+        if (c < P) {
+            float y0[VEC], g0[VEC];
+            ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+            incoming(c, g0);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(g0[k], y0[k], acc[k]);
+        }
+    }
+    tile_reduce<VEC, false>(acc, s_red, s_col);
     if (!ok) return;
-    const float dot = s_col[tx];
+    float dot[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) dot[k] = s_col[hwl * VEC + k];
     float* out = grad_z + base;
-    for (int c = ty; c < P; c += TRAIN_TY)
-        __stcs(out + static_cast<size_t>(c) * HW, yp[static_cast<size_t>(c) * HW] * (incoming(c) - dot));
+    int c = cg;
+    for (; c + CG < P; c += 2 * CG) {
+        float y0[VEC], y1[VEC], g0[VEC], g1[VEC];
+        ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+        ldv<VEC>(yp + static_cast<size_t>(c + CG) * HW, y1);
+        incoming(c, g0);
+        incoming(c + CG, g1);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) g0[k] = y0[k] * (g0[k] - dot[k]);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) g1[k] = y1[k] * (g1[k] - dot[k]);
+        stv_cs<VEC>(out + static_cast<size_t>(c) * HW, g0);
+        stv_cs<VEC>(out + static_cast<size_t>(c + CG) * HW, g1);
+    }
+    if (c < P) {
+        float y0[VEC], g0[VEC];
+        ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+        incoming(c, g0);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) g0[k] = y0[k] * (g0[k] - dot[k]);
+        stv_cs<VEC>(out + static_cast<size_t>(c) * HW, g0);
+    }
 }
 
 }  // namespace cpn

@@ -75,7 +75,7 @@ def _loss_call(pf, pooled, out, ys, mult, B, P, HW, K, flags, grads=True):
 
 # (B pairs, P, H, W, K): the cfg2 training map at a small batch, the ResNet-50 map, ragged tiles, one position
 @pytest.mark.parametrize("shape", [(4, 768, 26, 26, 200), (3, 2048, 7, 7, 196), (2, 33, 5, 9, 11), (5, 16, 24, 24, 9),
-                                   (2, 7, 1, 1, 3), (1, 130, 6, 11, 1000)])
+                                   (2, 7, 1, 1, 3), (1, 130, 6, 11, 1000), (2, 33, 5, 8, 4), (3, 5, 2, 2, 2)])
 @pytest.mark.parametrize("flags", [(False, False, True), (True, False, True), (False, True, True), (False, False, False)])
 def test_pipnet_loss_c_abi_matches_oracle(cuda_device, shape, flags):
     B, P, H, W, K = shape
@@ -149,7 +149,8 @@ def test_backward_scales_by_the_incoming_gradient(cuda_device):
 
 
 @pytest.mark.parametrize("mode", ["max", "sum"])
-@pytest.mark.parametrize("shape", [(4, 768, 26, 26), (3, 2048, 7, 7), (2, 33, 5, 9), (6, 16, 24, 24), (2, 7, 1, 1)])
+@pytest.mark.parametrize("shape", [(4, 768, 26, 26), (3, 2048, 7, 7), (2, 33, 5, 9), (6, 16, 24, 24), (2, 7, 1, 1),
+                                   (2, 33, 5, 8), (3, 5, 2, 2), (2, 130, 6, 22)])
 def test_softmax_pool_head_forward_backward(cuda_device, mode, shape):
     g = torch.Generator().manual_seed(sum(shape))
     z = torch.randn(*shape, generator=g) * 3
@@ -174,21 +175,62 @@ def test_softmax_pool_head_forward_backward(cuda_device, mode, shape):
         assert rel(zd2.grad.cpu().numpy(), o.numpy()) <= 1e-4
 
 
-def test_max_pool_ties_route_to_the_first_position(cuda_device):
-    """Equal columns give equal softmax values at several positions; AdaptiveMaxPool2d's backward picks the first."""
-    N, P, H, W = 2, 5, 3, 4
-    col = torch.randn(N, P, 1, 1, generator=torch.Generator().manual_seed(3))
+@pytest.mark.parametrize("hw", [(3, 4), (3, 3), (5, 8), (7, 7)])
+def test_max_pool_ties_route_to_the_first_position(cuda_device, hw):
+    """Equal columns give equal softmax values at several positions; AdaptiveMaxPool2d's backward picks the first.
+    Both lane layouts (H*W % 4 == 0 and not) and maps wider than one 32-position tile."""
+    N, P, (H, W) = 2, 5, hw
+    g = torch.Generator().manual_seed(3)
+    col = torch.randn(N, P, 1, 1, generator=g)
     z = col.expand(N, P, H, W).contiguous()
+    gpl = torch.randn(N, P, generator=g)
     pf = torch.empty(N, P, H, W, device=cuda_device)
     pooled = torch.empty(N, P, device=cuda_device)
     arg = torch.full((N, P), -1, device=cuda_device, dtype=torch.int32)
     ws = torch.empty(ops.softmax_pool_nchw_ws_floats(N, P, H * W), device=cuda_device)
     ops.softmax_pool_nchw(z.to(cuda_device), _lib.POOL_MAX, pf, pooled, arg, ws)
     assert int(arg.abs().max()) == 0
-    o = RL.head_gradients(z, "max", None, torch.ones(N, P))
+    o = RL.head_gradients(z, "max", None, gpl)
+    assert float(o[:, :, 0, 0].abs().max()) > 1e-3 and float(o.flatten(2)[:, :, 1:].abs().max()) == 0.0
     gz = torch.empty_like(pf)
-    ops.softmax_pool_nchw_bwd(pf, None, torch.ones(N, P, device=cuda_device), arg, _lib.POOL_MAX, gz)
+    ops.softmax_pool_nchw_bwd(pf, None, gpl.to(cuda_device), arg, _lib.POOL_MAX, gz)
     assert rel(gz.cpu().numpy(), o.numpy()) <= 1e-4
+
+
+def test_unaligned_maps_take_the_scalar_lane_layout(cuda_device):
+    """A map whose base is not 16-byte aligned (a view into a larger buffer) cannot use 128-bit accesses."""
+    B, P, H, W, K = 2, 24, 6, 6, 5
+    pf, pooled, out, ys, mult = (t.to(cuda_device) for t in make_inputs(B=B, P=P, H=H, W=W, K=K, is_count=False, mult=1.1,
+                                                                       seed=21))
+    n = pf.numel()
+    store_in, store_g = torch.empty(n + 1, device=cuda_device), torch.empty(n + 1, device=cuda_device)
+    pf_u = store_in[1:].view_as(pf)
+    pf_u.copy_(pf)
+    g_u = store_g[1:].view_as(pf)
+    assert pf_u.data_ptr() % 16 == 4 and pf_u.is_contiguous()
+    res_a, res_u = torch.empty(8, device=cuda_device), torch.empty(8, device=cuda_device)
+    ws = torch.empty(ops.pipnet_loss_ws_floats(B, P, H * W), device=cuda_device)
+    g_a, gpl, go = torch.empty_like(pf), torch.empty_like(pooled), torch.empty_like(out)
+    ops.pipnet_loss(pf, pooled, out, ys, mult, B, P, H * W, K, 5., 2., 2., 1., 1e-8, False, False, True, g_a, gpl, go, res_a, ws)
+    ops.pipnet_loss(pf_u, pooled, out, ys, mult, B, P, H * W, K, 5., 2., 2., 1., 1e-8, False, False, True, g_u, gpl, go,
+                    res_u, ws)
+    torch.testing.assert_close(res_u, res_a, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(g_u, g_a, rtol=1e-5, atol=1e-9)
+    z = torch.randn(2 * B, P, H, W, device=cuda_device)
+    z_u = store_in[1:].view_as(pf)
+    z_u.copy_(z)
+    outs = []
+    for src in (z, z_u):
+        y, pl = torch.empty_like(z), torch.empty(2 * B, P, device=cuda_device)
+        arg = torch.empty(2 * B, P, device=cuda_device, dtype=torch.int32)
+        ws2 = torch.empty(ops.softmax_pool_nchw_ws_floats(2 * B, P, H * W), device=cuda_device)
+        ops.softmax_pool_nchw(src, _lib.POOL_MAX, y, pl, arg, ws2)
+        gz = store_g[1:].view_as(pf) if src is z_u else torch.empty_like(z)
+        ops.softmax_pool_nchw_bwd(y, None, pl, arg, _lib.POOL_MAX, gz)
+        outs.append((y.clone(), pl.clone(), arg.clone(), gz.clone()))
+    torch.testing.assert_close(outs[1][0], outs[0][0], rtol=1e-6, atol=1e-9)
+    assert torch.equal(outs[1][2], outs[0][2])
+    torch.testing.assert_close(outs[1][3], outs[0][3], rtol=1e-5, atol=1e-9)
 
 
 def _train_step(model, x, ys, is_count, kernels_on):
