@@ -34,7 +34,7 @@ inline int threads_of(int vec, int P) {
 inline int tanh_blocks(int P) { return (P + 127) / 128; }
 
 struct LossWs {  // layout of the caller's workspace, in floats
-    long long align, tanh, row_loss, row_gmult, row_correct, total;
+    long long align, tanh, row_loss, row_gmult, row_correct, ticket, total;
 };
 LossWs loss_ws(int B, int P, int HW) {
     LossWs w;
@@ -43,7 +43,8 @@ LossWs loss_ws(int B, int P, int HW) {
     w.row_loss = w.tanh + 2LL * tanh_blocks(P);
     w.row_gmult = w.row_loss + 2LL * B;
     w.row_correct = w.row_gmult + 2LL * B;
-    w.total = w.row_correct + 2LL * B;
+    w.ticket = w.row_correct + 2LL * B;
+    w.total = w.ticket + 1;
     return w;
 }
 
@@ -77,30 +78,39 @@ extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     set_info("pipnet_loss", 4.0 * B * P * HW, (grad_pf ? 16.0 : 8.0) * B * P * HW);
 
+    // launch 1: the pass over the map (also zeroes the ticket); launch 2: every other term + the weighting
     const int vec = vec_of(HW, {proto_features, grad_pf});
     const float align_scale = static_cast<float>(-0.5 * align_w / n_patches);
+    unsigned* ticket = reinterpret_cast<unsigned*>(workspace + w.ticket);
     if (vec == 4)
         cpn::align_loss_kernel<4><<<dim3(tiles, B), threads_of(4, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
-                                                                               B, P, HW, align_eps, align_scale);
+                                                                               ticket, B, P, HW, align_eps, align_scale);
     else
         cpn::align_loss_kernel<1><<<dim3(tiles, B), threads_of(1, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
-                                                                               B, P, HW, align_eps, align_scale);
+                                                                               ticket, B, P, HW, align_eps, align_scale);
     CPN_CUDA(cudaGetLastError());
-    cpn::tanh_loss_kernel<<<dim3(tanh_blocks(P), 2), 128, 0, st>>>(pooled, grad_pooled, workspace + w.tanh, B, P,
-                                                                    tanh_coeff, eps_tanh,
-                                                                    static_cast<float>(-0.5 * tanh_w / P));
-    CPN_CUDA(cudaGetLastError());
-    if (!pretrain) {
-        cpn::class_loss_kernel<<<2 * B, 128, 0, st>>>(out, ys, norm_mult, use_log1p, grad_out, workspace + w.row_loss,
-                                                      workspace + w.row_gmult, workspace + w.row_correct, B, K,
-                                                      static_cast<float>(class_w / (2.0 * B)));
-        CPN_CUDA(cudaGetLastError());
-    }
-    cpn::loss_finalize_kernel<<<1, 256, 0, st>>>(workspace + w.align, B * tiles, workspace + w.tanh, tanh_blocks(P),
-                                                 workspace + w.row_loss, workspace + w.row_gmult,
-                                                 workspace + w.row_correct, 2 * B, static_cast<float>(n_patches),
-                                                 static_cast<float>(P), align_w, tanh_w, class_w, pretrain, finetune,
-                                                 result);
+    cpn::LossTermsArgs a;
+    a.pooled = pooled;
+    a.out = out;
+    a.ys = ys;
+    a.mult = norm_mult;
+    a.grad_pooled = grad_pooled;
+    a.grad_out = grad_out;
+    a.align_partial = workspace + w.align;
+    a.tanh_partial = workspace + w.tanh;
+    a.row_loss = workspace + w.row_loss;
+    a.row_gmult = workspace + w.row_gmult;
+    a.row_correct = workspace + w.row_correct;
+    a.ticket = ticket;
+    a.result = result;
+    a.B = B, a.P = P, a.K = K, a.n_align = B * tiles, a.tanh_blocks = tanh_blocks(P);
+    a.use_log1p = use_log1p, a.pretrain = pretrain, a.finetune = finetune;
+    a.coeff = tanh_coeff, a.eps = eps_tanh;
+    a.tanh_scale = static_cast<float>(-0.5 * tanh_w / P);
+    a.class_scale = static_cast<float>(class_w / (2.0 * B));
+    a.n_patches = static_cast<float>(n_patches);
+    a.align_w = align_w, a.tanh_w = tanh_w, a.class_w = class_w;
+    cpn::loss_terms_kernel<<<2 * tanh_blocks(P) + (pretrain ? 0 : 2 * B), 128, 0, st>>>(a);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }
@@ -134,12 +144,23 @@ extern "C" int cpn_softmax_pool_nchw(const float* z, int mode, float* proto_feat
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     set_info("softmax_pool_nchw", 0.0, 8.0 * N * P * HW);
     int* idx = mode == CPN_POOL_MAX ? part_idx : nullptr;
-    if (vec_of(HW, {z, proto_features}) == 4)
-        cpn::softmax_pool_nchw_kernel<4><<<dim3(tiles, N), threads_of(4, P), 0, st>>>(z, proto_features, part_val, idx,
-                                                                                      mode == CPN_POOL_SUM, P, HW);
-    else
-        cpn::softmax_pool_nchw_kernel<1><<<dim3(tiles, N), threads_of(1, P), 0, st>>>(z, proto_features, part_val, idx,
-                                                                                      mode == CPN_POOL_SUM, P, HW);
+    const int vec = vec_of(HW, {z, proto_features});
+    const dim3 grid(tiles, N);
+    const int threads = threads_of(vec, P), sum = mode == CPN_POOL_SUM;
+    // the [P, 32] tile of z in shared memory when two CTAs of it fit one SM (P <= 768)
+    const size_t tile_bytes = static_cast<size_t>(P) * cpn::TRAIN_TILE * sizeof(float);
+    const bool cache = tile_bytes <= 96 * 1024;
+    if (cache && vec == 4) {
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<4, true>, tile_bytes));
+        cpn::softmax_pool_nchw_kernel<4, true><<<grid, threads, tile_bytes, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+    } else if (cache) {
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<1, true>, tile_bytes));
+        cpn::softmax_pool_nchw_kernel<1, true><<<grid, threads, tile_bytes, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+    } else if (vec == 4) {
+        cpn::softmax_pool_nchw_kernel<4, false><<<grid, threads, 0, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+    } else {
+        cpn::softmax_pool_nchw_kernel<1, false><<<grid, threads, 0, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+    }
     CPN_CUDA(cudaGetLastError());
     cpn::pool_fold_nchw_kernel<<<dim3((P + 127) / 128, N), 128, 0, st>>>(part_val, part_idx, mode == CPN_POOL_SUM, pooled,
                                                                         argmax, P, tiles);

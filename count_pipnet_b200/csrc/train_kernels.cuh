@@ -5,10 +5,9 @@
 //
 //   reference                                            kernel
 //   pipnet/train.py:253-265 align_loss (both directions)  align_loss_kernel
-//   pipnet/train.py:198-201 tanh loss                      tanh_loss_kernel
-//   pipnet/train.py:216-222 log1p(out^m) + log_softmax
-//     + NLLLoss(mean), :233-235 accuracy                   class_loss_kernel
-//   pipnet/train.py:212-229 weighting of the terms         loss_finalize_kernel
+//   pipnet/train.py:198-201 tanh loss,
+//     :216-222 log1p(out^m) + log_softmax + NLLLoss(mean),
+//     :233-235 accuracy, :212-229 weighting of the terms   loss_terms_kernel (one launch, last CTA finalises)
 //   pipnet/pipnet.py:96,105 Softmax(dim=1) + max pool,
 //     pipnet/count_pipnet.py:88 spatial sum                softmax_pool_nchw_kernel, pool_fold_nchw_kernel
 //   their autograd backward                                softmax_pool_nchw_bwd_kernel
@@ -85,16 +84,18 @@ __device__ __forceinline__ void tile_reduce(float (&acc)[VEC], float (*s_red)[TR
 // loss = -mean_n log(d_n + eps) (the two directions of train.py:173 have the same value); d loss / d pf1 = grad_scale *
 // pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
 // grid = (ceil(HW / 32), B), block = (32 / VEC) * channel groups. partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
+// Also zeroes the ticket of loss_terms_kernel.
 template <int VEC>
 __global__ void __launch_bounds__(TRAIN_THREADS, 2)
-    align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial, int B, int P,
-                      int HW, float eps, float grad_scale) {
+    align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial,
+                      unsigned* __restrict__ ticket, int B, int P, int HW, float eps, float grad_scale) {
     constexpr int L = 32 / VEC;
     constexpr int U = VEC == 4 ? 2 : 4;  // channels in flight per thread and view
     __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
     __shared__ float s_col[TRAIN_TILE];
     const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
     const int b = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
+    if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) *ticket = 0u;  // for loss_terms_kernel, the next launch of the stream
     const bool ok = hw0 < HW;
     const size_t img = static_cast<size_t>(P) * HW;
     const size_t off1 = static_cast<size_t>(b) * img + hw0, off2 = off1 + static_cast<size_t>(B) * img;
@@ -176,39 +177,10 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     }
 }
 
-// ---- tanh loss ------------------------------------------------------------------------------------------------------
-// pooled [2B, P]; for each view: t_p = tanh(sum_b coeff * pooled[b, p]), loss term = log(t_p + eps).
-// grid = (ceil(P / 128), 2), block = 128. partial [2 * gridDim.x] = per-CTA sum of log(t + eps).
-// d loss / d pooled[b, p] = grad_scale * coeff * (1 - t^2) / (t + eps), grad_scale = -tanh_weight / (2 P).
-__global__ void __launch_bounds__(128)
-    tanh_loss_kernel(const float* __restrict__ pooled, float* __restrict__ grad, float* __restrict__ partial, int B, int P,
-                     float coeff, float eps, float grad_scale) {
-    __shared__ float s_part[4];
-    const int view = blockIdx.y, p = blockIdx.x * 128 + threadIdx.x;
-    const float* src = pooled + static_cast<size_t>(view) * B * P + p;
-    float l = 0.f;
-    if (p < P) {
-        float s = 0.f;
-        for (int b = 0; b < B; ++b) s = __fadd_rn(s, __fmul_rn(coeff, src[static_cast<size_t>(b) * P]));
-        const float t = tanhf(s);
-        l = logf(t + eps);
-        if (grad != nullptr) {
-            const float g = grad_scale * coeff * (1.f - t * t) / (t + eps);
-            float* dst = grad + static_cast<size_t>(view) * B * P + p;
-            for (int b = 0; b < B; ++b) dst[static_cast<size_t>(b) * P] = g;
-        }
-    }
-    l = warp_sum(l);
-    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l;
-    __syncthreads();
-    if (threadIdx.x == 0) partial[view * gridDim.x + blockIdx.x] = (s_part[0] + s_part[1]) + (s_part[2] + s_part[3]);
-}
-
-// ---- classification loss --------------------------------------------------------------------------------------------
-// out [2B, K], ys [B] (labels of the pairs: train.py:169 ys = cat(ys1, ys1)), mult = the classifier's
-// normalization_multiplier (one float on the device). v = use_log1p ? log1p(out^mult) : out; loss_i = -log_softmax(v)[y].
-// One CTA of 128 threads per row. Writes grad_out (scaled by grad_scale = class_weight / 2B), and per row: the loss,
-// the multiplier's gradient, whether arg-max(out) == y (first index on ties, as torch.argmax on CUDA).
+// ---- tanh loss, classification loss, weighting: ONE launch ------------------------------------------------------------
+// loss_terms_kernel: grid = 2 * ceil(P / 128) tanh CTAs + (pretrain ? 0 : 2B) classification CTAs, 128 threads each; the
+// CTA that takes the last ticket sums every partial array in a fixed order and writes result[8] (so the values do not
+// depend on which CTA that is). The ticket is zeroed by align_loss_kernel, which the stream runs before this kernel.
 struct ValIdx {
     float v;
     int i;
@@ -227,16 +199,67 @@ __device__ __forceinline__ ValIdx warp_argmax(ValIdx a) {
     return a;
 }
 
-__global__ void __launch_bounds__(128)
-    class_loss_kernel(const float* __restrict__ out, const long long* __restrict__ ys, const float* __restrict__ mult,
-                      int use_log1p, float* __restrict__ grad_out, float* __restrict__ row_loss,
-                      float* __restrict__ row_gmult, float* __restrict__ row_correct, int B, int K, float grad_scale) {
-    __shared__ float s_f[4];
-    __shared__ ValIdx s_vi[4];
-    const int i = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const float* o = out + static_cast<size_t>(i) * K;
-    const int y = static_cast<int>(ys[i % B]);
-    const float m = use_log1p ? mult[0] : 1.f;
+struct LossTermsArgs {
+    const float* pooled;      // [2B, P]
+    const float* out;         // [2B, K]
+    const long long* ys;      // [B]
+    const float* mult;        // [1]
+    float* grad_pooled;       // [2B, P] or null
+    float* grad_out;          // [2B, K] or null
+    const float* align_partial;  // [n_align], written by align_loss_kernel
+    float* tanh_partial;      // [2 * tanh_blocks]
+    float* row_loss;          // [2B]
+    float* row_gmult;         // [2B]
+    float* row_correct;       // [2B]
+    unsigned* ticket;
+    float* result;            // [8]
+    int B, P, K, n_align, tanh_blocks;
+    int use_log1p, pretrain, finetune;
+    float coeff, eps, tanh_scale, class_scale;  // tanh_scale = -tanh_w / (2P), class_scale = class_w / 2B
+    float n_patches, align_w, tanh_w, class_w;
+};
+
+// pooled [2B, P]; for each view: t_p = tanh(sum_b coeff * pooled[b, p]), loss term = log(t_p + eps) (train.py:198-201);
+// d loss / d pooled[b, p] = tanh_scale * coeff * (1 - t^2) / (t + eps). One CTA = 128 prototypes of one view.
+__device__ __forceinline__ void tanh_terms(const LossTermsArgs& a, int view, int pblock, float* s_f) {
+    const int p = pblock * 128 + threadIdx.x;
+    const float* src = a.pooled + static_cast<size_t>(view) * a.B * a.P + p;
+    float l = 0.f;
+    if (p < a.P) {
+        float s = 0.f;
+        int b = 0;
+        for (; b + 8 <= a.B; b += 8) {  // eight loads in flight, summed in image order
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = src[static_cast<size_t>(b + j) * a.P];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s = __fadd_rn(s, __fmul_rn(a.coeff, v[j]));
+        }
+        for (; b < a.B; ++b) s = __fadd_rn(s, __fmul_rn(a.coeff, src[static_cast<size_t>(b) * a.P]));
+        const float t = tanhf(s);
+        l = logf(t + a.eps);
+        if (a.grad_pooled != nullptr) {
+            const float g = a.tanh_scale * a.coeff * (1.f - t * t) / (t + a.eps);
+            float* dst = a.grad_pooled + static_cast<size_t>(view) * a.B * a.P + p;
+            for (b = 0; b < a.B; ++b) dst[static_cast<size_t>(b) * a.P] = g;
+        }
+    }
+    l = warp_sum(l);
+    if ((threadIdx.x & 31) == 0) s_f[threadIdx.x >> 5] = l;
+    __syncthreads();
+    if (threadIdx.x == 0) a.tanh_partial[view * a.tanh_blocks + pblock] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
+}
+
+// out [2B, K], ys [B] (labels of the pairs: train.py:169 ys = cat(ys1, ys1)), mult = the classifier's
+// normalization_multiplier. v = use_log1p ? log1p(out^mult) : out; loss_i = -log_softmax(v)[y] (train.py:216-222).
+// One CTA per row: grad_out (scaled by class_scale) and per row the loss, the multiplier's gradient, whether
+// arg-max(out) == y (train.py:233-235; first index on ties, as torch.argmax on CUDA).
+__device__ __forceinline__ void class_terms(const LossTermsArgs& a, int i, float* s_f, ValIdx* s_vi) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, K = a.K;
+    const float* o = a.out + static_cast<size_t>(i) * K;
+    const int y = static_cast<int>(a.ys[i % a.B]);
+    const bool use_log1p = a.use_log1p != 0;
+    const float m = use_log1p ? a.mult[0] : 1.f;
     auto value = [&](float x) { return use_log1p ? log1pf(powf(x, m)) : x; };
 
     float vmax = -INFINITY;
@@ -267,11 +290,11 @@ __global__ void __launch_bounds__(128)
     __syncthreads();
 
     float gm = 0.f;
-    if (grad_out != nullptr) {
-        float* g = grad_out + static_cast<size_t>(i) * K;
+    if (a.grad_out != nullptr) {
+        float* g = a.grad_out + static_cast<size_t>(i) * K;
         for (int k = tid; k < K; k += 128) {
             const float x = o[k];
-            const float gv = (expf(value(x) - lse) - (k == y ? 1.f : 0.f)) * grad_scale;
+            const float gv = (expf(value(x) - lse) - (k == y ? 1.f : 0.f)) * a.class_scale;
             if (use_log1p) {
                 // d log1p(x^m) / dx = m x^(m-1) / (1 + x^m); d / dm = x^m log(x) / (1 + x^m), 0 at x == 0 (torch's pow
                 // backward: zero where the base is 0 and the exponent >= 0)
@@ -288,58 +311,70 @@ __global__ void __launch_bounds__(128)
     if (lane == 0) s_f[warp] = gm;
     __syncthreads();
     if (tid == 0) {
-        row_loss[i] = (y >= 0 && y < K) ? lse - value(o[y]) : 0.f;
-        row_gmult[i] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
-        row_correct[i] = best.i == y ? 1.f : 0.f;
+        a.row_loss[i] = (y >= 0 && y < K) ? lse - value(o[y]) : 0.f;
+        a.row_gmult[i] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
+        a.row_correct[i] = best.i == y ? 1.f : 0.f;
     }
 }
 
-// ---- finalize -------------------------------------------------------------------------------------------------------
-// One CTA of 256 threads: fixed-order sums of the partial arrays, then train.py:212-229's weighting.
-// result[0] align, [1] tanh, [2] class, [3] loss, [4] number of correct predictions, [5] d loss / d multiplier, [6..7] 0.
-__device__ __forceinline__ float block_sum_256(const float* __restrict__ v, int n, float* s_red) {
-    float a = 0.f;
-    for (int i = threadIdx.x; i < n; i += 256) a += v[i];
-    a = warp_sum(a);
-    __syncthreads();  // s_red may still be read from the previous call
-    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = a;
+// Fixed-order sum of v[0..n) by a CTA of 128 threads; v was written by other CTAs of this or an earlier launch (read
+// through L2).
+__device__ __forceinline__ float block_sum_128(const float* v, int n, float* s_f) {
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < n; i += 128) acc += __ldcg(v + i);
+    acc = warp_sum(acc);
+    __syncthreads();  // s_f may still be read from the previous call
+    if ((threadIdx.x & 31) == 0) s_f[threadIdx.x >> 5] = acc;
     __syncthreads();
-    float t = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) t += s_red[w];
-    return t;
+    return (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
 }
 
-__global__ void __launch_bounds__(256)
-    loss_finalize_kernel(const float* __restrict__ align_partial, int n_align, const float* __restrict__ tanh_partial,
-                         int n_tanh_per_view, const float* __restrict__ row_loss, const float* __restrict__ row_gmult,
-                         const float* __restrict__ row_correct, int rows, float n_patches, float n_protos,
-                         float align_w, float tanh_w, float class_w, int pretrain, int finetune,
-                         float* __restrict__ result) {
-    __shared__ float s_red[8];
-    const float a = block_sum_256(align_partial, n_align, s_red) / n_patches;
-    const float t1 = block_sum_256(tanh_partial, n_tanh_per_view, s_red) / n_protos;
-    const float t2 = block_sum_256(tanh_partial + n_tanh_per_view, n_tanh_per_view, s_red) / n_protos;
+// train.py:212-229's weighting. result[0] align, [1] tanh, [2] class, [3] loss, [4] number of correct predictions,
+// [5] d loss / d multiplier, [6..7] 0.
+__device__ __forceinline__ void finalize_terms(const LossTermsArgs& a, float* s_f) {
+    const float al = block_sum_128(a.align_partial, a.n_align, s_f) / a.n_patches;
+    const float t1 = block_sum_128(a.tanh_partial, a.tanh_blocks, s_f) / static_cast<float>(a.P);
+    const float t2 = block_sum_128(a.tanh_partial + a.tanh_blocks, a.tanh_blocks, s_f) / static_cast<float>(a.P);
     float cl = 0.f, gm = 0.f, correct = 0.f;
-    if (!pretrain) {
-        cl = block_sum_256(row_loss, rows, s_red) / static_cast<float>(rows);
-        gm = block_sum_256(row_gmult, rows, s_red);
-        correct = block_sum_256(row_correct, rows, s_red);
+    if (!a.pretrain) {
+        cl = block_sum_128(a.row_loss, 2 * a.B, s_f) / static_cast<float>(2 * a.B);
+        gm = block_sum_128(a.row_gmult, 2 * a.B, s_f);
+        correct = block_sum_128(a.row_correct, 2 * a.B, s_f);
     }
     if (threadIdx.x == 0) {
         const float th = -(t1 + t2) / 2.f;
         float loss = 0.f;
-        if (!finetune) loss = align_w * a + tanh_w * th;
-        if (!pretrain) loss = finetune ? class_w * cl : loss + class_w * cl;
-        result[0] = a;
-        result[1] = th;
-        result[2] = cl;
-        result[3] = loss;
-        result[4] = correct;
-        result[5] = gm;
-        result[6] = 0.f;
-        result[7] = 0.f;
+        if (!a.finetune) loss = a.align_w * al + a.tanh_w * th;
+        if (!a.pretrain) loss = a.finetune ? a.class_w * cl : loss + a.class_w * cl;
+        a.result[0] = al;
+        a.result[1] = th;
+        a.result[2] = cl;
+        a.result[3] = loss;
+        a.result[4] = correct;
+        a.result[5] = gm;
+        a.result[6] = 0.f;
+        a.result[7] = 0.f;
     }
+}
+
+__global__ void __launch_bounds__(128) loss_terms_kernel(const LossTermsArgs a) {
+    __shared__ float s_f[4];
+    __shared__ ValIdx s_vi[4];
+    __shared__ int s_last;
+    const int n_tanh = 2 * a.tanh_blocks;
+    if (static_cast<int>(blockIdx.x) < n_tanh)
+        tanh_terms(a, blockIdx.x / a.tanh_blocks, blockIdx.x % a.tanh_blocks, s_f);
+    else
+        class_terms(a, blockIdx.x - n_tanh, s_f, s_vi);
+    // both roles end with thread 0 writing this CTA's partials: publish them, then take a ticket
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    finalize_terms(a, s_f);
 }
 
 // buf *= *scale unless *scale == 1 (the usual loss.backward() case costs one tiny launch and no pass over memory).
@@ -351,21 +386,27 @@ __global__ void scale_unless_one_kernel(float* __restrict__ buf, long long n, co
 }
 
 // ---- softmax over prototypes + spatial pooling on an NCHW map, forward ------------------------------------------------
-// exp(x) for x <= 0 as one FMUL + MUFU.EX2 (relative error < 1e-6 for the entries that matter, x > -10).
-__device__ __forceinline__ float exp_neg(float x) {
+// 2^x as one MUFU.EX2: exp(x - m) = 2^((x - m) * log2e); the subtraction first keeps the error independent of the size of
+// the logits (relative error < 1e-6 for the entries that matter, x - m > -10).
+__device__ __forceinline__ float ex2_approx(float x) {
     float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
 
 // z [N, P, HW] -> pf [N, P, HW] = softmax over P per position; per-CTA pooling partials over its 32 positions:
 // part_val [N, tiles, P] (max or sum), part_idx [N, tiles, P] (position of the maximum, lowest on ties; max mode only).
 // grid = (tiles = ceil(HW / 32), N), block = (32 / VEC) * channel groups.
-template <int VEC>
+// CACHE: the CTA's [P, 32] tile of z is kept in dynamic shared memory (P * 128 bytes, two CTAs per SM up to P = 768), so
+// z is read from global memory once instead of three times; every thread reads back only what it wrote itself (a warp
+// writes 512 contiguous bytes: no bank conflicts, no barrier). Without it passes 2 and 3 re-read the tile from L2.
+template <int VEC, bool CACHE>
 __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     softmax_pool_nchw_kernel(const float* __restrict__ z, float* __restrict__ pf, float* __restrict__ part_val,
                              int* __restrict__ part_idx, int mode_sum, int P, int HW) {
     constexpr int L = 32 / VEC;
+    constexpr int U = VEC == 4 ? 4 : 8;  // loads in flight per thread in the first pass
+    extern __shared__ __align__(16) float s_tile[];  // [P][32] when CACHE
     __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
     __shared__ float s_col[TRAIN_TILE];
     const int tid = threadIdx.x, lane = tid & 31, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
@@ -373,21 +414,35 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     const bool ok = hw0 < HW;
     const size_t base = static_cast<size_t>(n) * P * HW + hw0;
     const float* zp = z + base;
+    float* mine = s_tile + hwl * VEC;  // + c * 32
+    auto reload = [&](int c, float (&x)[VEC]) {
+        if constexpr (CACHE) {
+            ldv<VEC>(mine + c * TRAIN_TILE, x);
+        } else {
+            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+        }
+    };
 
-    float m[VEC], s[VEC], x[VEC];
+    float m[VEC], s[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k) m[k] = -INFINITY;
     if (ok) {
         int c = cg;
-        for (; c + CG < P; c += 2 * CG) {
-            float x2[VEC];
-            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-            ldv<VEC>(zp + static_cast<size_t>(c + CG) * HW, x2);
+        for (; c + (U - 1) * CG < P; c += U * CG) {
+            float x[U][VEC];
 #pragma unroll
-            for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], fmaxf(x[k], x2[k]));
+            for (int u = 0; u < U; ++u) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if constexpr (CACHE) stv<VEC>(mine + (c + u * CG) * TRAIN_TILE, x[u]);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[u][k]);
+            }
         }
-        if (c < P) {
+        for (; c < P; c += CG) {
+            float x[VEC];
             ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+            if constexpr (CACHE) stv<VEC>(mine + c * TRAIN_TILE, x);
 #pragma unroll
             for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
         }
@@ -399,20 +454,11 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
         s[k] = 0.f;
     }
     if (ok) {
-        int c = cg;
-        for (; c + CG < P; c += 2 * CG) {
-            float x2[VEC];
-            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-            ldv<VEC>(zp + static_cast<size_t>(c + CG) * HW, x2);
+        for (int c = cg; c < P; c += CG) {
+            float x[VEC];
+            reload(c, x);
 #pragma unroll
-            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x[k] - m[k]);
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x2[k] - m[k]);
-        }
-        if (c < P) {
-            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) s[k] += exp_neg(x[k] - m[k]);
+            for (int k = 0; k < VEC; ++k) s[k] += ex2_approx((x[k] - m[k]) * 1.4426950408889634f);
         }
     }
     tile_reduce<VEC, false>(s, s_red, s_col);
@@ -431,10 +477,11 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
 #pragma unroll
         for (int k = 0; k < VEC; ++k) y[k] = 0.f;
         if (ok) {
-            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+            float x[VEC];
+            reload(c, x);
 #pragma unroll
-            for (int k = 0; k < VEC; ++k) y[k] = exp_neg(x[k] - m[k]) * inv[k];
-            stv<VEC>(op + static_cast<size_t>(c) * HW, y);
+            for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
+            stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
         }
         if (mode_sum) {
             float t = y[0];
