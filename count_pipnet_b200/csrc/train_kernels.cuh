@@ -414,10 +414,12 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     const bool ok = hw0 < HW;
     const size_t base = static_cast<size_t>(n) * P * HW + hw0;
     const float* zp = z + base;
-    float* mine = s_tile + hwl * VEC;  // + c * 32
+    // this thread's slot in row c of the tile: 16-byte groups XOR-swizzled with the row number, so that the pooling phase
+    // (thread = channel row, all 32 positions) reads rows 128 bytes apart without bank conflicts
+    auto slot = [&](int c) { return s_tile + c * TRAIN_TILE + ((((hwl * VEC) >> 2) ^ (c & 7)) << 2) + ((hwl * VEC) & 3); };
     auto reload = [&](int c, float (&x)[VEC]) {
         if constexpr (CACHE) {
-            ldv<VEC>(mine + c * TRAIN_TILE, x);
+            ldv<VEC>(slot(c), x);
         } else {
             ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
         }
@@ -434,7 +436,7 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
             for (int u = 0; u < U; ++u) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                if constexpr (CACHE) stv<VEC>(mine + (c + u * CG) * TRAIN_TILE, x[u]);
+                if constexpr (CACHE) stv<VEC>(slot(c + u * CG), x[u]);
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[u][k]);
             }
@@ -442,7 +444,7 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
         for (; c < P; c += CG) {
             float x[VEC];
             ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-            if constexpr (CACHE) stv<VEC>(mine + c * TRAIN_TILE, x);
+            if constexpr (CACHE) stv<VEC>(slot(c), x);
 #pragma unroll
             for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
         }
@@ -469,41 +471,84 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     float* op = pf + base;
     float* pv = part_val + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
     int* pi = part_idx == nullptr ? nullptr : part_idx + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
-    // the L lanes that share a channel row reduce among themselves; they also share the loop's trip count
-    unsigned gmask = 0xffffffffu;
-    if constexpr (L < 32) gmask = ((1u << L) - 1u) << (lane & ~(L - 1));
-    for (int c = cg; c < P; c += CG) {
-        float y[VEC];
+    if constexpr (CACHE) {
+        // pass 3: probabilities out to global memory and back into the thread's own slots (zeros beyond the map's edge) ...
+        for (int c = cg; c < P; c += CG) {
+            float y[VEC];
 #pragma unroll
-        for (int k = 0; k < VEC; ++k) y[k] = 0.f;
-        if (ok) {
-            float x[VEC];
-            reload(c, x);
+            for (int k = 0; k < VEC; ++k) y[k] = 0.f;
+            if (ok) {
+                float x[VEC];
+                ldv<VEC>(slot(c), x);
 #pragma unroll
-            for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
-            stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
+                for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
+                stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
+            }
+            stv<VEC>(slot(c), y);
         }
-        if (mode_sum) {
-            float t = y[0];
+        __syncthreads();
+        // ... then thread = channel row: max (first position on ties) or sum over the tile's 32 positions, in position order
+        for (int c = tid; c < P; c += blockDim.x) {
+            const float* row = s_tile + c * TRAIN_TILE;
+            float v[TRAIN_TILE];
 #pragma unroll
-            for (int k = 1; k < VEC; ++k) t += y[k];
+            for (int j = 0; j < TRAIN_TILE / 4; ++j) {
+                const float4 t = *reinterpret_cast<const float4*>(row + ((j ^ (c & 7)) << 2));
+                v[4 * j] = t.x, v[4 * j + 1] = t.y, v[4 * j + 2] = t.z, v[4 * j + 3] = t.w;
+            }
+            if (mode_sum) {
+                float t = v[0];
 #pragma unroll
-            for (int o = L / 2; o > 0; o >>= 1) t += __shfl_xor_sync(gmask, t, o);
-            if (hwl == 0) pv[c] = t;
-        } else {
-            // probabilities are >= 0, so their bit patterns order like the values: one integer REDUX per channel row
-            float lm = y[0];
+                for (int j = 1; j < TRAIN_TILE; ++j) t += v[j];
+                pv[c] = t;
+            } else {
+                float best = v[0];
 #pragma unroll
-            for (int k = 1; k < VEC; ++k) lm = fmaxf(lm, y[k]);
-            const unsigned bits = __float_as_uint(lm);
-            const unsigned mx = __reduce_max_sync(gmask, bits);
-            const unsigned vote = __ballot_sync(gmask, ok && bits == mx);
-            if (lane == __ffs(vote) - 1) {  // first lane = lowest position among equal maxima
-                int kk = 0;
+                for (int j = 1; j < TRAIN_TILE; ++j) best = fmaxf(best, v[j]);
+                int idx = 0;
 #pragma unroll
-                for (int k = VEC - 1; k >= 0; --k) kk = (y[k] == lm) ? k : kk;
-                pv[c] = lm;
-                pi[c] = hw0 + kk;
+                for (int j = TRAIN_TILE - 1; j >= 0; --j) idx = (v[j] == best) ? j : idx;
+                pv[c] = best;
+                pi[c] = blockIdx.x * TRAIN_TILE + idx;
+            }
+        }
+    } else {
+        // the L lanes that share a channel row reduce among themselves; they also share the loop's trip count
+        unsigned gmask = 0xffffffffu;
+        if constexpr (L < 32) gmask = ((1u << L) - 1u) << (lane & ~(L - 1));
+        for (int c = cg; c < P; c += CG) {
+            float y[VEC];
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) y[k] = 0.f;
+            if (ok) {
+                float x[VEC];
+                ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
+                stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
+            }
+            if (mode_sum) {
+                float t = y[0];
+#pragma unroll
+                for (int k = 1; k < VEC; ++k) t += y[k];
+#pragma unroll
+                for (int o = L / 2; o > 0; o >>= 1) t += __shfl_xor_sync(gmask, t, o);
+                if (hwl == 0) pv[c] = t;
+            } else {
+                // probabilities are >= 0, so their bit patterns order like the values: one integer REDUX per channel row
+                float lm = y[0];
+#pragma unroll
+                for (int k = 1; k < VEC; ++k) lm = fmaxf(lm, y[k]);
+                const unsigned bits = __float_as_uint(lm);
+                const unsigned mx = __reduce_max_sync(gmask, bits);
+                const unsigned vote = __ballot_sync(gmask, ok && bits == mx);
+                if (lane == __ffs(vote) - 1) {  // first lane = lowest position among equal maxima
+                    int kk = 0;
+#pragma unroll
+                    for (int k = VEC - 1; k >= 0; --k) kk = (y[k] == lm) ? k : kk;
+                    pv[c] = lm;
+                    pi[c] = hw0 + kk;
+                }
             }
         }
     }
