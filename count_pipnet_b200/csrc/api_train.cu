@@ -147,19 +147,23 @@ extern "C" int cpn_softmax_pool_nchw(const float* z, int mode, float* proto_feat
     const int vec = vec_of(HW, {z, proto_features});
     const dim3 grid(tiles, N);
     const int threads = threads_of(vec, P), sum = mode == CPN_POOL_SUM;
-    // the [P, 32] tile of z in shared memory when two CTAs of it fit one SM (P <= 768)
+    // the [P, 32] tile of z in shared memory when two CTAs of it fit one SM (P <= 768), else 512 staging rows
     const size_t tile_bytes = static_cast<size_t>(P) * cpn::TRAIN_TILE * sizeof(float);
     const bool cache = tile_bytes <= 96 * 1024;
+    const size_t smem = cache ? tile_bytes
+                              : static_cast<size_t>(P < cpn::STAGE_ROWS ? P : cpn::STAGE_ROWS) * cpn::TRAIN_TILE * sizeof(float);
     if (cache && vec == 4) {
-        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<4, true>, tile_bytes));
-        cpn::softmax_pool_nchw_kernel<4, true><<<grid, threads, tile_bytes, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<4, true>, smem));
+        cpn::softmax_pool_nchw_kernel<4, true><<<grid, threads, smem, st>>>(z, proto_features, part_val, idx, sum, P, HW);
     } else if (cache) {
-        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<1, true>, tile_bytes));
-        cpn::softmax_pool_nchw_kernel<1, true><<<grid, threads, tile_bytes, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<1, true>, smem));
+        cpn::softmax_pool_nchw_kernel<1, true><<<grid, threads, smem, st>>>(z, proto_features, part_val, idx, sum, P, HW);
     } else if (vec == 4) {
-        cpn::softmax_pool_nchw_kernel<4, false><<<grid, threads, 0, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<4, false>, smem));
+        cpn::softmax_pool_nchw_kernel<4, false><<<grid, threads, smem, st>>>(z, proto_features, part_val, idx, sum, P, HW);
     } else {
-        cpn::softmax_pool_nchw_kernel<1, false><<<grid, threads, 0, st>>>(z, proto_features, part_val, idx, sum, P, HW);
+        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_kernel<1, false>, smem));
+        cpn::softmax_pool_nchw_kernel<1, false><<<grid, threads, smem, st>>>(z, proto_features, part_val, idx, sum, P, HW);
     }
     CPN_CUDA(cudaGetLastError());
     cpn::pool_fold_nchw_kernel<<<dim3((P + 127) / 128, N), 128, 0, st>>>(part_val, part_idx, mode == CPN_POOL_SUM, pooled,

@@ -397,19 +397,21 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // z [N, P, HW] -> pf [N, P, HW] = softmax over P per position; per-CTA pooling partials over its 32 positions:
 // part_val [N, tiles, P] (max or sum), part_idx [N, tiles, P] (position of the maximum, lowest on ties; max mode only).
 // grid = (tiles = ceil(HW / 32), N), block = (32 / VEC) * channel groups.
+constexpr int STAGE_ROWS = 512;  // 64 KB of staging rows per CTA when the whole tile does not fit
 // CACHE: the CTA's [P, 32] tile of z is kept in dynamic shared memory (P * 128 bytes, two CTAs per SM up to P = 768), so
 // z is read from global memory once instead of three times; every thread reads back only what it wrote itself (a warp
-// writes 512 contiguous bytes: no bank conflicts, no barrier). Without it passes 2 and 3 re-read the tile from L2.
+// writes 512 contiguous bytes: no bank conflicts, no barrier). Without it passes 2 and 3 re-read the tile from L2 and the
+// probabilities are staged STAGE_ROWS channel rows at a time for the pooling phase.
 template <int VEC, bool CACHE>
 __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     softmax_pool_nchw_kernel(const float* __restrict__ z, float* __restrict__ pf, float* __restrict__ part_val,
                              int* __restrict__ part_idx, int mode_sum, int P, int HW) {
     constexpr int L = 32 / VEC;
     constexpr int U = VEC == 4 ? 4 : 8;  // loads in flight per thread in the first pass
-    extern __shared__ __align__(16) float s_tile[];  // [P][32] when CACHE
+    extern __shared__ __align__(16) float s_tile[];  // [P][32] when CACHE, else [min(P, STAGE_ROWS)][32] staging rows
     __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
     __shared__ float s_col[TRAIN_TILE];
-    const int tid = threadIdx.x, lane = tid & 31, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
+    const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
     const int n = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
     const bool ok = hw0 < HW;
     const size_t base = static_cast<size_t>(n) * P * HW + hw0;
@@ -471,36 +473,39 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     float* op = pf + base;
     float* pv = part_val + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
     int* pi = part_idx == nullptr ? nullptr : part_idx + (static_cast<size_t>(n) * gridDim.x + blockIdx.x) * P;
-    if constexpr (CACHE) {
-        // pass 3: probabilities out to global memory and back into the thread's own slots (zeros beyond the map's edge) ...
-        for (int c = cg; c < P; c += CG) {
+    // pass 3, in chunks of `rows` channel rows (all P rows when the tile is cached): probabilities out to global memory and
+    // into the thread's own slots of the staging rows (zeros beyond the map's edge); then thread = channel row: max (first
+    // position on ties) or sum over the tile's 32 positions, in position order.
+    const int rows = CACHE ? P : (P < STAGE_ROWS ? P : STAGE_ROWS);
+    for (int c0 = 0; c0 < P; c0 += rows) {
+        const int c1 = c0 + rows < P ? c0 + rows : P;
+        for (int c = c0 + cg; c < c1; c += CG) {
             float y[VEC];
 #pragma unroll
             for (int k = 0; k < VEC; ++k) y[k] = 0.f;
             if (ok) {
                 float x[VEC];
-                ldv<VEC>(slot(c), x);
+                reload(c, x);
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
                 stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
             }
-            stv<VEC>(slot(c), y);
+            stv<VEC>(slot(c - c0), y);
         }
         __syncthreads();
-        // ... then thread = channel row: max (first position on ties) or sum over the tile's 32 positions, in position order
-        for (int c = tid; c < P; c += blockDim.x) {
-            const float* row = s_tile + c * TRAIN_TILE;
+        for (int r = tid; r < c1 - c0; r += blockDim.x) {
+            const float* row = s_tile + r * TRAIN_TILE;
             float v[TRAIN_TILE];
 #pragma unroll
             for (int j = 0; j < TRAIN_TILE / 4; ++j) {
-                const float4 t = *reinterpret_cast<const float4*>(row + ((j ^ (c & 7)) << 2));
+                const float4 t = *reinterpret_cast<const float4*>(row + ((j ^ (r & 7)) << 2));
                 v[4 * j] = t.x, v[4 * j + 1] = t.y, v[4 * j + 2] = t.z, v[4 * j + 3] = t.w;
             }
             if (mode_sum) {
                 float t = v[0];
 #pragma unroll
                 for (int j = 1; j < TRAIN_TILE; ++j) t += v[j];
-                pv[c] = t;
+                pv[c0 + r] = t;
             } else {
                 float best = v[0];
 #pragma unroll
@@ -508,49 +513,11 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
                 int idx = 0;
 #pragma unroll
                 for (int j = TRAIN_TILE - 1; j >= 0; --j) idx = (v[j] == best) ? j : idx;
-                pv[c] = best;
-                pi[c] = blockIdx.x * TRAIN_TILE + idx;
+                pv[c0 + r] = best;
+                pi[c0 + r] = blockIdx.x * TRAIN_TILE + idx;
             }
         }
-    } else {
-        // the L lanes that share a channel row reduce among themselves; they also share the loop's trip count
-        unsigned gmask = 0xffffffffu;
-        if constexpr (L < 32) gmask = ((1u << L) - 1u) << (lane & ~(L - 1));
-        for (int c = cg; c < P; c += CG) {
-            float y[VEC];
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) y[k] = 0.f;
-            if (ok) {
-                float x[VEC];
-                ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-#pragma unroll
-                for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
-                stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
-            }
-            if (mode_sum) {
-                float t = y[0];
-#pragma unroll
-                for (int k = 1; k < VEC; ++k) t += y[k];
-#pragma unroll
-                for (int o = L / 2; o > 0; o >>= 1) t += __shfl_xor_sync(gmask, t, o);
-                if (hwl == 0) pv[c] = t;
-            } else {
-                // probabilities are >= 0, so their bit patterns order like the values: one integer REDUX per channel row
-                float lm = y[0];
-#pragma unroll
-                for (int k = 1; k < VEC; ++k) lm = fmaxf(lm, y[k]);
-                const unsigned bits = __float_as_uint(lm);
-                const unsigned mx = __reduce_max_sync(gmask, bits);
-                const unsigned vote = __ballot_sync(gmask, ok && bits == mx);
-                if (lane == __ffs(vote) - 1) {  // first lane = lowest position among equal maxima
-                    int kk = 0;
-#pragma unroll
-                    for (int k = VEC - 1; k >= 0; --k) kk = (y[k] == lm) ? k : kk;
-                    pv[c] = lm;
-                    pi[c] = hw0 + kk;
-                }
-            }
-        }
+        if (c1 < P) __syncthreads();  // the next chunk overwrites the staging rows
     }
 }
 

@@ -75,7 +75,8 @@ def _loss_call(pf, pooled, out, ys, mult, B, P, HW, K, flags, grads=True):
 
 # (B pairs, P, H, W, K): the cfg2 training map at a small batch, the ResNet-50 map, ragged tiles, one position
 @pytest.mark.parametrize("shape", [(4, 768, 26, 26, 200), (3, 2048, 7, 7, 196), (2, 33, 5, 9, 11), (5, 16, 24, 24, 9),
-                                   (2, 7, 1, 1, 3), (1, 130, 6, 11, 1000), (2, 33, 5, 8, 4), (3, 5, 2, 2, 2)])
+                                   (2, 7, 1, 1, 3), (1, 130, 6, 11, 1000), (2, 33, 5, 8, 4), (3, 5, 2, 2, 2),
+                                   (1, 2048, 28, 28, 196)])
 @pytest.mark.parametrize("flags", [(False, False, True), (True, False, True), (False, True, True), (False, False, False)])
 def test_pipnet_loss_c_abi_matches_oracle(cuda_device, shape, flags):
     B, P, H, W, K = shape
@@ -150,7 +151,8 @@ def test_backward_scales_by_the_incoming_gradient(cuda_device):
 
 @pytest.mark.parametrize("mode", ["max", "sum"])
 @pytest.mark.parametrize("shape", [(4, 768, 26, 26), (3, 2048, 7, 7), (2, 33, 5, 9), (6, 16, 24, 24), (2, 7, 1, 1),
-                                   (2, 33, 5, 8), (3, 5, 2, 2), (2, 130, 6, 22)])
+                                   (2, 33, 5, 8), (3, 5, 2, 2), (2, 130, 6, 22), (2, 2048, 28, 28), (1, 1100, 4, 8),
+                                   (2, 800, 3, 3)])
 def test_softmax_pool_head_forward_backward(cuda_device, mode, shape):
     g = torch.Generator().manual_seed(sum(shape))
     z = torch.randn(*shape, generator=g) * 3

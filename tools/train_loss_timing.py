@@ -22,7 +22,7 @@ from count_pipnet_b200.pipnet import train as T  # noqa: E402
 
 SHAPES = [  # name, image pairs B, P, H, W, K, pooling
     ("cfg2 PIP-Net ConvNeXt-26 224^2, 64 pairs", 64, 768, 26, 26, 200, "max"),
-    ("cfg3 PIP-Net ResNet-50 224^2, 64 pairs", 64, 2048, 7, 7, 196, "max"),
+    ("cfg3 PIP-Net ResNet-50 224^2, 32 pairs", 32, 2048, 28, 28, 196, "max"),
     ("cfg1 Count-PIP-Net 192^2, 64 pairs", 64, 16, 24, 24, 9, "sum"),
     ("cfg5 PIP-Net 448^2, 16 pairs", 16, 768, 54, 54, 200, "max"),
 ]
