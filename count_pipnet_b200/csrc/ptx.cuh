@@ -140,6 +140,9 @@ __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
 __device__ __forceinline__ void cp_async4(uint32_t smem_dst, const void* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
 }
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {  // 16-byte aligned both sides; skips L1
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {

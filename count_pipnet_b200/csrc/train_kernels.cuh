@@ -430,23 +430,41 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     float m[VEC], s[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k) m[k] = -INFINITY;
-    if (ok) {
+    if constexpr (CACHE) {
+        // the whole tile in flight at once: every thread copies its own slots global -> shared (LDGSTS, no registers held),
+        // waits for its own copies only, then takes the maximum from shared memory
+        if (ok) {
+            for (int c = cg; c < P; c += CG) {
+                if constexpr (VEC == 4)
+                    ptx::cp_async16(ptx::smem_u32(slot(c)), zp + static_cast<size_t>(c) * HW);
+                else
+                    ptx::cp_async4(ptx::smem_u32(slot(c)), zp + static_cast<size_t>(c) * HW);
+            }
+        }
+        ptx::cp_async_commit();
+        ptx::cp_async_wait<0>();
+        if (ok) {
+            for (int c = cg; c < P; c += CG) {
+                float x[VEC];
+                ldv<VEC>(slot(c), x);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
+            }
+        }
+    } else if (ok) {
         int c = cg;
         for (; c + (U - 1) * CG < P; c += U * CG) {
             float x[U][VEC];
 #pragma unroll
             for (int u = 0; u < U; ++u) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                if constexpr (CACHE) stv<VEC>(slot(c + u * CG), x[u]);
+            for (int u = 0; u < U; ++u)
 #pragma unroll
                 for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[u][k]);
-            }
         }
         for (; c < P; c += CG) {
             float x[VEC];
             ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-            if constexpr (CACHE) stv<VEC>(slot(c), x);
 #pragma unroll
             for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
         }
