@@ -416,10 +416,34 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": f"{n_img} images x 4 timed forwards (1 warm-up) of the same workload through "
                                               "oracle/ (CPU restatement of the reference forward)"}
+            line["train_head"] = train_head_block(args, cfg, B, device)
         print(json.dumps(line), file=JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# prototype-map shape (P, H, W) of each config's training forward; "sum" = Count-PIP-Net pooling
+TRAIN_MAPS = {"cfg1": (16, 24, 24, "sum"), "cfg2": (768, 26, 26, "max"), "cfg3": (2048, 28, 28, "max"),
+              "cfg4": (16, 24, 24, "sum"), "cfg5": (768, 54, 54, "max")}
+
+
+def train_head_block(args, cfg, batch, device):
+    """Not part of `value`: the training-side head kernels (pipnet/train.py mirror: loss + all gradients in one call,
+    softmax + pooling forward / backward on the NCHW map) timed alone at this config's map shape for `batch` images =
+    batch / 2 pairs, next to the same arithmetic as stock PyTorch ops on this GPU."""
+    try:
+        from count_pipnet_b200.pipnet.train_timing import time_train_head
+        P, H, W, mode = TRAIN_MAPS[args.config]
+        r = time_train_head(max(1, batch // 2), P, H, W, cfg["classes"], mode, iters=10, device=device)
+        peak = load_peaks()["hbm_gbs"]
+        out = {"shape": f"[{2 * max(1, batch // 2)}, {P}, {H}, {W}] fp32 NCHW, pooling {mode}", "unit": "ms",
+               "note": "CUDA events, L2 flushed between iterations; frac = algorithmic bytes / time / measured HBM peak"}
+        for op, d in r.items():
+            out[op] = {"ms": round(d["ms"], 4), "frac": round(d["gbs"] / peak, 3), "eager_ms": round(d["eager_ms"], 4)}
+        return out
+    except Exception as e:  # never lose the bench line over the extra block
+        return {"error": repr(e)}
 
 
 def ncu_traffic(kernel, detail):

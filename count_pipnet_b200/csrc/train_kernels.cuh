@@ -388,6 +388,7 @@ __global__ void scale_unless_one_kernel(float* __restrict__ buf, long long n, co
 // ---- softmax over prototypes + spatial pooling on an NCHW map, forward ------------------------------------------------
 // 2^x as one MUFU.EX2: exp(x - m) = 2^((x - m) * log2e); the subtraction first keeps the error independent of the size of
 // the logits (relative error < 1e-6 for the entries that matter, x - m > -10).
+constexpr float LOG2E = 1.4426950408889634f;
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -451,36 +452,65 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
                 for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
             }
         }
-    } else if (ok) {
-        int c = cg;
-        for (; c + (U - 1) * CG < P; c += U * CG) {
-            float x[U][VEC];
-#pragma unroll
-            for (int u = 0; u < U; ++u) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[u][k]);
-        }
-        for (; c < P; c += CG) {
-            float x[VEC];
-            ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) m[k] = fmaxf(m[k], x[k]);
-        }
     }
-    tile_reduce<VEC, true>(m, s_red, s_col);
+    if constexpr (CACHE) {
+        tile_reduce<VEC, true>(m, s_red, s_col);
 #pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-        m[k] = s_col[hwl * VEC + k];
-        s[k] = 0.f;
-    }
-    if (ok) {
-        for (int c = cg; c < P; c += CG) {
-            float x[VEC];
-            reload(c, x);
+        for (int k = 0; k < VEC; ++k) {
+            m[k] = s_col[hwl * VEC + k];
+            s[k] = 0.f;
+        }
+        if (ok) {
+            for (int c = cg; c < P; c += CG) {
+                float x[VEC];
+                ldv<VEC>(slot(c), x);
 #pragma unroll
-            for (int k = 0; k < VEC; ++k) s[k] += ex2_approx((x[k] - m[k]) * 1.4426950408889634f);
+                for (int k = 0; k < VEC; ++k) s[k] += ex2_approx((x[k] - m[k]) * LOG2E);
+            }
+        }
+    } else {
+        // one pass over global memory for both the maximum and the sum: running maximum per thread, the sum rescaled when
+        // it moves (U loads in flight, U + 1 exponentials per U values); then the threads' (m, s) pairs are merged
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) s[k] = 0.f;
+        if (ok) {
+            int c = cg;
+            for (; c + (U - 1) * CG < P; c += U * CG) {
+                float x[U][VEC];
+#pragma unroll
+                for (int u = 0; u < U; ++u) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    float mn = m[k];
+#pragma unroll
+                    for (int u = 0; u < U; ++u) mn = fmaxf(mn, x[u][k]);
+                    float acc = s[k] * ex2_approx((m[k] - mn) * LOG2E);
+#pragma unroll
+                    for (int u = 0; u < U; ++u) acc += ex2_approx((x[u][k] - mn) * LOG2E);
+                    s[k] = acc;
+                    m[k] = mn;
+                }
+            }
+            for (; c < P; c += CG) {
+                float x[VEC];
+                ldv<VEC>(zp + static_cast<size_t>(c) * HW, x);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const float mn = fmaxf(m[k], x[k]);
+                    s[k] = s[k] * ex2_approx((m[k] - mn) * LOG2E) + ex2_approx((x[k] - mn) * LOG2E);
+                    m[k] = mn;
+                }
+            }
+        }
+        float mt[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) mt[k] = m[k];
+        tile_reduce<VEC, true>(m, s_red, s_col);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            m[k] = s_col[hwl * VEC + k];
+            // a thread without channels (or beyond the map's edge) has mt = -inf and s = 0: keep it 0, not 0 * 2^(-inf - -inf)
+            s[k] = s[k] == 0.f ? 0.f : s[k] * ex2_approx((mt[k] - m[k]) * LOG2E);
         }
     }
     tile_reduce<VEC, false>(s, s_red, s_col);
@@ -497,7 +527,28 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     const int rows = CACHE ? P : (P < STAGE_ROWS ? P : STAGE_ROWS);
     for (int c0 = 0; c0 < P; c0 += rows) {
         const int c1 = c0 + rows < P ? c0 + rows : P;
-        for (int c = c0 + cg; c < c1; c += CG) {
+        int c = c0 + cg;
+        if constexpr (!CACHE) {  // global loads U at a time
+            for (; c + (U - 1) * CG < c1; c += U * CG) {
+                float x[U][VEC];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) x[u][k] = 0.f;
+                    if (ok) ldv<VEC>(zp + static_cast<size_t>(c + u * CG) * HW, x[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (ok) {
+#pragma unroll
+                        for (int k = 0; k < VEC; ++k) x[u][k] = ex2_approx((x[u][k] - m[k]) * LOG2E) * inv[k];
+                        stv_cs<VEC>(op + static_cast<size_t>(c + u * CG) * HW, x[u]);
+                    }
+                    stv<VEC>(slot(c + u * CG - c0), x[u]);
+                }
+            }
+        }
+        for (; c < c1; c += CG) {
             float y[VEC];
 #pragma unroll
             for (int k = 0; k < VEC; ++k) y[k] = 0.f;
@@ -505,7 +556,7 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
                 float x[VEC];
                 reload(c, x);
 #pragma unroll
-                for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * 1.4426950408889634f) * inv[k];
+                for (int k = 0; k < VEC; ++k) y[k] = ex2_approx((x[k] - m[k]) * LOG2E) * inv[k];
                 stv_cs<VEC>(op + static_cast<size_t>(c) * HW, y);
             }
             stv<VEC>(slot(c - c0), y);
