@@ -6,7 +6,6 @@
 #include "train_kernels.cuh"
 
 #include <cstdint>
-#include <cstdlib>
 #include <initializer_list>
 
 using namespace cpn_api;
@@ -33,14 +32,6 @@ inline int threads_of(int vec, int P) {
     return threads;
 }
 inline int tanh_blocks(int P) { return (P + 127) / 128; }
-// A/B switch for the shared-memory-tile variants of the loss kernel (CPN_TRAIN_CACHE=0: the L2 re-read variant).
-inline bool train_cache_enabled() {
-    static const bool on = [] {
-        const char* e = getenv("CPN_TRAIN_CACHE");
-        return !(e != nullptr && e[0] == '0');
-    }();
-    return on;
-}
 
 struct LossWs {  // layout of the caller's workspace, in floats
     long long align, tanh, row_loss, row_gmult, row_correct, ticket, total;
@@ -91,27 +82,12 @@ extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled,
     const int vec = vec_of(HW, {proto_features, grad_pf});
     const float align_scale = static_cast<float>(-0.5 * align_w / n_patches);
     unsigned* ticket = reinterpret_cast<unsigned*>(workspace + w.ticket);
-    // both views' tiles in shared memory (cp.async, one CTA per SM) when they fit: P <= 880
-    const size_t tiles_bytes = 2 * static_cast<size_t>(P) * cpn::TRAIN_TILE * sizeof(float);
-    const bool cache = tiles_bytes <= 220 * 1024 && train_cache_enabled();
-    const dim3 agrid(tiles, B);
-    const int athreads = threads_of(vec, P);
-    float* apart = workspace + w.align;
-    if (cache && vec == 4) {
-        CPN_CUDA(ensure_smem(cpn::align_loss_kernel<4, true>, tiles_bytes));
-        cpn::align_loss_kernel<4, true><<<agrid, athreads, tiles_bytes, st>>>(proto_features, grad_pf, apart, ticket, B, P, HW,
-                                                                             align_eps, align_scale);
-    } else if (cache) {
-        CPN_CUDA(ensure_smem(cpn::align_loss_kernel<1, true>, tiles_bytes));
-        cpn::align_loss_kernel<1, true><<<agrid, athreads, tiles_bytes, st>>>(proto_features, grad_pf, apart, ticket, B, P, HW,
-                                                                             align_eps, align_scale);
-    } else if (vec == 4) {
-        cpn::align_loss_kernel<4, false><<<agrid, athreads, 0, st>>>(proto_features, grad_pf, apart, ticket, B, P, HW,
-                                                                    align_eps, align_scale);
-    } else {
-        cpn::align_loss_kernel<1, false><<<agrid, athreads, 0, st>>>(proto_features, grad_pf, apart, ticket, B, P, HW,
-                                                                    align_eps, align_scale);
-    }
+    if (vec == 4)
+        cpn::align_loss_kernel<4><<<dim3(tiles, B), threads_of(4, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
+                                                                               ticket, B, P, HW, align_eps, align_scale);
+    else
+        cpn::align_loss_kernel<1><<<dim3(tiles, B), threads_of(1, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
+                                                                               ticket, B, P, HW, align_eps, align_scale);
     CPN_CUDA(cudaGetLastError());
     cpn::LossTermsArgs a;
     a.pooled = pooled;
@@ -206,27 +182,12 @@ extern "C" int cpn_softmax_pool_nchw_bwd(const float* proto_features, const floa
     if (N <= 0 || N > 65535 || P <= 0 || HW <= 0) return fail("cpn_softmax_pool_nchw_bwd: bad N=%d P=%d HW=%d", N, P, HW);
     set_info("softmax_pool_nchw_bwd", 0.0, (grad_pf ? 12.0 : 8.0) * N * P * HW);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int vec = vec_of(HW, {proto_features, grad_pf, grad_z});
-    const dim3 grid(tiles_of(HW), N);
-    const int threads = threads_of(vec, P), sum = mode == CPN_POOL_SUM;
-    // the tiles of pf and grad_pf in shared memory (cp.async, one CTA per SM) when they fit
-    const size_t tiles_bytes = (grad_pf ? 2 : 1) * static_cast<size_t>(P) * cpn::TRAIN_TILE * sizeof(float);
-    const bool cache = tiles_bytes <= 220 * 1024 && train_cache_enabled();
-    if (cache && vec == 4) {
-        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_bwd_kernel<4, true>, tiles_bytes));
-        cpn::softmax_pool_nchw_bwd_kernel<4, true><<<grid, threads, tiles_bytes, st>>>(proto_features, grad_pf, grad_pooled,
-                                                                                      argmax, sum, grad_z, P, HW);
-    } else if (cache) {
-        CPN_CUDA(ensure_smem(cpn::softmax_pool_nchw_bwd_kernel<1, true>, tiles_bytes));
-        cpn::softmax_pool_nchw_bwd_kernel<1, true><<<grid, threads, tiles_bytes, st>>>(proto_features, grad_pf, grad_pooled,
-                                                                                      argmax, sum, grad_z, P, HW);
-    } else if (vec == 4) {
-        cpn::softmax_pool_nchw_bwd_kernel<4, false><<<grid, threads, 0, st>>>(proto_features, grad_pf, grad_pooled, argmax,
-                                                                             sum, grad_z, P, HW);
-    } else {
-        cpn::softmax_pool_nchw_bwd_kernel<1, false><<<grid, threads, 0, st>>>(proto_features, grad_pf, grad_pooled, argmax,
-                                                                             sum, grad_z, P, HW);
-    }
+    if (vec_of(HW, {proto_features, grad_pf, grad_z}) == 4)
+        cpn::softmax_pool_nchw_bwd_kernel<4><<<dim3(tiles_of(HW), N), threads_of(4, P), 0, st>>>(
+            proto_features, grad_pf, grad_pooled, argmax, mode == CPN_POOL_SUM, grad_z, P, HW);
+    else
+        cpn::softmax_pool_nchw_bwd_kernel<1><<<dim3(tiles_of(HW), N), threads_of(1, P), 0, st>>>(
+            proto_features, grad_pf, grad_pooled, argmax, mode == CPN_POOL_SUM, grad_z, P, HW);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }

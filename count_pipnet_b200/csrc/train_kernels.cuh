@@ -85,15 +85,12 @@ __device__ __forceinline__ void tile_reduce(float (&acc)[VEC], float (*s_red)[TR
 // pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
 // grid = (ceil(HW / 32), B), block = (32 / VEC) * channel groups. partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
 // Also zeroes the ticket of loss_terms_kernel.
-// CACHE: both views' [P, 32] tiles are copied into dynamic shared memory with cp.async (2 * P * 128 bytes: one CTA per SM,
-// P <= 880), all of it in flight at once, and the gradient pass reads them from there instead of from L2.
-template <int VEC, bool CACHE>
-__global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
     align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial,
                       unsigned* __restrict__ ticket, int B, int P, int HW, float eps, float grad_scale) {
     constexpr int L = 32 / VEC;
     constexpr int U = VEC == 4 ? 2 : 4;  // channels in flight per thread and view
-    extern __shared__ __align__(16) float s_tile[];  // CACHE: view 1 rows [P][32], then view 2 rows [P][32]
     __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
     __shared__ float s_col[TRAIN_TILE];
     const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
@@ -104,29 +101,6 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
     const size_t off1 = static_cast<size_t>(b) * img + hw0, off2 = off1 + static_cast<size_t>(B) * img;
     const float* p1 = pf + off1;
     const float* p2 = pf + off2;
-    float* s1 = s_tile + hwl * VEC;                      // + c * 32: this thread's slot of row c, view 1
-    float* s2 = s1 + static_cast<size_t>(P) * TRAIN_TILE;  // view 2
-    auto load1 = [&](int c, float (&x)[VEC]) {
-        if constexpr (CACHE) ldv<VEC>(s1 + c * TRAIN_TILE, x); else ldv<VEC>(p1 + static_cast<size_t>(c) * HW, x);
-    };
-    auto load2 = [&](int c, float (&x)[VEC]) {
-        if constexpr (CACHE) ldv<VEC>(s2 + c * TRAIN_TILE, x); else ldv<VEC>(p2 + static_cast<size_t>(c) * HW, x);
-    };
-    if constexpr (CACHE) {
-        if (ok) {
-            for (int c = cg; c < P; c += CG) {
-                if constexpr (VEC == 4) {
-                    ptx::cp_async16(ptx::smem_u32(s1 + c * TRAIN_TILE), p1 + static_cast<size_t>(c) * HW);
-                    ptx::cp_async16(ptx::smem_u32(s2 + c * TRAIN_TILE), p2 + static_cast<size_t>(c) * HW);
-                } else {
-                    ptx::cp_async4(ptx::smem_u32(s1 + c * TRAIN_TILE), p1 + static_cast<size_t>(c) * HW);
-                    ptx::cp_async4(ptx::smem_u32(s2 + c * TRAIN_TILE), p2 + static_cast<size_t>(c) * HW);
-                }
-            }
-        }
-        ptx::cp_async_commit();
-        ptx::cp_async_wait<0>();  // own copies only: every thread reads back what it copied itself
-    }
     float acc[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
@@ -136,8 +110,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
             float a[U][VEC], v[U][VEC];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                load1(c + u * CG, a[u]);
-                load2(c + u * CG, v[u]);
+                ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+                ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
             }
 #pragma unroll
             for (int u = 0; u < U; ++u)
@@ -146,8 +120,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
         }
         for (; c < P; c += CG) {
             float a[VEC], v[VEC];
-            load1(c, a);
-            load2(c, v);
+            ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+            ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
 #pragma unroll
             for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[k], v[k], acc[k]);
         }
@@ -173,8 +147,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
         float a[U][VEC], v[U][VEC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            load1(c + u * CG, a[u]);
-            load2(c + u * CG, v[u]);
+            ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+            ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -190,8 +164,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
     }
     for (; c < P; c += CG) {
         float a[VEC], v[VEC];
-        load1(c, a);
-        load2(c, v);
+        ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+        ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
 #pragma unroll
         for (int k = 0; k < VEC; ++k) {
             const float t = a[k];
@@ -641,10 +615,8 @@ __global__ void __launch_bounds__(128)
 // g[c] = grad_pf[n, c, hw] (0 if grad_pf == nullptr) + grad_pooled[n, c] * (sum mode ? 1 : hw == argmax[n, c]);
 // grad_z = pf * (g - sum_c g * pf)   (softmax backward of the sum of both incoming gradients).
 // grid = (ceil(HW / 32), N), block = (32 / VEC) * channel groups.
-// CACHE: the [P, 32] tiles of pf and (if given) grad_pf are copied into dynamic shared memory with cp.async, all in flight
-// at once, and both passes read them from there.
-template <int VEC, bool CACHE>
-__global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
     softmax_pool_nchw_bwd_kernel(const float* __restrict__ pf, const float* __restrict__ grad_pf,
                                  const float* __restrict__ grad_pooled, const int* __restrict__ argmax, int mode_sum,
                                  float* __restrict__ grad_z, int P, int HW) {
@@ -659,30 +631,9 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
     const float* gp = grad_pf == nullptr ? nullptr : grad_pf + base;
     const float* gpool = grad_pooled == nullptr ? nullptr : grad_pooled + static_cast<size_t>(n) * P;
     const int* am = (argmax == nullptr || mode_sum) ? nullptr : argmax + static_cast<size_t>(n) * P;
-    extern __shared__ __align__(16) float s_tile[];         // CACHE: pf rows [P][32], then grad_pf rows [P][32]
-    float* sy = s_tile + hwl * VEC;                         // + c * 32: this thread's slot of row c
-    float* sg = sy + static_cast<size_t>(P) * TRAIN_TILE;
-    if constexpr (CACHE) {
-        if (ok) {
-            for (int c = cg; c < P; c += CG) {
-                if constexpr (VEC == 4) {
-                    ptx::cp_async16(ptx::smem_u32(sy + c * TRAIN_TILE), yp + static_cast<size_t>(c) * HW);
-                    if (gp != nullptr) ptx::cp_async16(ptx::smem_u32(sg + c * TRAIN_TILE), gp + static_cast<size_t>(c) * HW);
-                } else {
-                    ptx::cp_async4(ptx::smem_u32(sy + c * TRAIN_TILE), yp + static_cast<size_t>(c) * HW);
-                    if (gp != nullptr) ptx::cp_async4(ptx::smem_u32(sg + c * TRAIN_TILE), gp + static_cast<size_t>(c) * HW);
-                }
-            }
-        }
-        ptx::cp_async_commit();
-        ptx::cp_async_wait<0>();  // own copies only: every thread reads back what it copied itself
-    }
-    auto load_y = [&](int c, float (&x)[VEC]) {
-        if constexpr (CACHE) ldv<VEC>(sy + c * TRAIN_TILE, x); else ldv<VEC>(yp + static_cast<size_t>(c) * HW, x);
-    };
     auto incoming = [&](int c, float (&g)[VEC]) {
         if (gp != nullptr) {
-            if constexpr (CACHE) ldv<VEC>(sg + c * TRAIN_TILE, g); else ldv<VEC>(gp + static_cast<size_t>(c) * HW, g);
+            ldv<VEC>(gp + static_cast<size_t>(c) * HW, g);
         } else {
 #pragma unroll
             for (int k = 0; k < VEC; ++k) g[k] = 0.f;
@@ -706,8 +657,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
         int c = cg;
         for (; c + CG < P; c += 2 * CG) {
             float y0[VEC], y1[VEC], g0[VEC], g1[VEC];
-            load_y(c, y0);
-            load_y(c + CG, y1);
+            ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+            ldv<VEC>(yp + static_cast<size_t>(c + CG) * HW, y1);
             incoming(c, g0);
             incoming(c + CG, g1);
 #pragma unroll
@@ -717,7 +668,7 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
         }
         if (c < P) {
             float y0[VEC], g0[VEC];
-            load_y(c, y0);
+            ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
             incoming(c, g0);
 #pragma unroll
             for (int k = 0; k < VEC; ++k) acc[k] = fmaf(g0[k], y0[k], acc[k]);
@@ -732,8 +683,8 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
     int c = cg;
     for (; c + CG < P; c += 2 * CG) {
         float y0[VEC], y1[VEC], g0[VEC], g1[VEC];
-        load_y(c, y0);
-        load_y(c + CG, y1);
+        ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
+        ldv<VEC>(yp + static_cast<size_t>(c + CG) * HW, y1);
         incoming(c, g0);
         incoming(c + CG, g1);
 #pragma unroll
@@ -745,7 +696,7 @@ __global__ void __launch_bounds__(TRAIN_THREADS, CACHE ? 1 : 2)
     }
     if (c < P) {
         float y0[VEC], g0[VEC];
-        load_y(c, y0);
+        ldv<VEC>(yp + static_cast<size_t>(c) * HW, y0);
         incoming(c, g0);
 #pragma unroll
         for (int k = 0; k < VEC; ++k) g0[k] = y0[k] * (g0[k] - dot[k]);
