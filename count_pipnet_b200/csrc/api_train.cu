@@ -78,18 +78,10 @@ extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     set_info("pipnet_loss", 4.0 * B * P * HW, (grad_pf ? 16.0 : 8.0) * B * P * HW);
 
-    // launch 1: the pass over the map (also zeroes the ticket); launch 2: every other term + the weighting
-    const int vec = vec_of(HW, {proto_features, grad_pf});
-    const float align_scale = static_cast<float>(-0.5 * align_w / n_patches);
-    unsigned* ticket = reinterpret_cast<unsigned*>(workspace + w.ticket);
-    if (vec == 4)
-        cpn::align_loss_kernel<4><<<dim3(tiles, B), threads_of(4, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
-                                                                               ticket, B, P, HW, align_eps, align_scale);
-    else
-        cpn::align_loss_kernel<1><<<dim3(tiles, B), threads_of(1, P), 0, st>>>(proto_features, grad_pf, workspace + w.align,
-                                                                               ticket, B, P, HW, align_eps, align_scale);
-    CPN_CUDA(cudaGetLastError());
+    // One kernel: the first CTAs do the tanh / classification terms on 128 threads while the others stream the map; the
+    // CTA that takes the last ticket does the weighting. The ticket is zeroed by a memset node ahead of it.
     cpn::LossTermsArgs a;
+    unsigned* ticket = reinterpret_cast<unsigned*>(workspace + w.ticket);
     a.pooled = pooled;
     a.out = out;
     a.ys = ys;
@@ -110,7 +102,20 @@ extern "C" int cpn_pipnet_loss(const float* proto_features, const float* pooled,
     a.class_scale = static_cast<float>(class_w / (2.0 * B));
     a.n_patches = static_cast<float>(n_patches);
     a.align_w = align_w, a.tanh_w = tanh_w, a.class_w = class_w;
-    cpn::loss_terms_kernel<<<2 * tanh_blocks(P) + (pretrain ? 0 : 2 * B), 128, 0, st>>>(a);
+    const int n_terms = 2 * tanh_blocks(P) + (pretrain ? 0 : 2 * B);
+    const long long ctas = static_cast<long long>(n_terms) + static_cast<long long>(tiles) * B;
+    if (ctas > 0x7fffffffLL) return fail("cpn_pipnet_loss: %lld CTAs", ctas);
+    const int vec = vec_of(HW, {proto_features, grad_pf});
+    const float align_scale = static_cast<float>(-0.5 * align_w / n_patches);
+    int threads = threads_of(vec, P);
+    if (threads < 128) threads = 128;  // the terms roles and the weighting run on 128 threads
+    CPN_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned), st));
+    if (vec == 4)
+        cpn::pipnet_loss_kernel<4><<<static_cast<unsigned>(ctas), threads, 0, st>>>(
+            proto_features, grad_pf, workspace + w.align, n_terms, tiles, B, P, HW, align_eps, align_scale, a);
+    else
+        cpn::pipnet_loss_kernel<1><<<static_cast<unsigned>(ctas), threads, 0, st>>>(
+            proto_features, grad_pf, workspace + w.align, n_terms, tiles, B, P, HW, align_eps, align_scale, a);
     CPN_CUDA(cudaGetLastError());
     return 0;
 }

@@ -4,10 +4,10 @@
 // runs give the same bits), no atomics.
 //
 //   reference                                            kernel
-//   pipnet/train.py:253-265 align_loss (both directions)  align_loss_kernel
+//   pipnet/train.py:253-265 align_loss (both directions)  pipnet_loss_kernel, map CTAs
 //   pipnet/train.py:198-201 tanh loss,
 //     :216-222 log1p(out^m) + log_softmax + NLLLoss(mean),
-//     :233-235 accuracy, :212-229 weighting of the terms   loss_terms_kernel (one launch, last CTA finalises)
+//     :233-235 accuracy, :212-229 weighting of the terms   pipnet_loss_kernel, terms CTAs + the last CTA
 //   pipnet/pipnet.py:96,105 Softmax(dim=1) + max pool,
 //     pipnet/count_pipnet.py:88 spatial sum                softmax_pool_nchw_kernel, pool_fold_nchw_kernel
 //   their autograd backward                                softmax_pool_nchw_bwd_kernel
@@ -79,108 +79,12 @@ __device__ __forceinline__ void tile_reduce(float (&acc)[VEC], float (*s_red)[TR
     __syncthreads();
 }
 
-// ---- align loss -----------------------------------------------------------------------------------------------------
-// pf [2B, P, HW]: view 1 = images [0, B), view 2 = images [B, 2B). For patch n = (b, hw): d_n = sum_c pf1 * pf2,
-// loss = -mean_n log(d_n + eps) (the two directions of train.py:173 have the same value); d loss / d pf1 = grad_scale *
-// pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
-// grid = (ceil(HW / 32), B), block = (32 / VEC) * channel groups. partial [B * gridDim.x] = per-CTA sum of -log(d + eps).
-// Also zeroes the ticket of loss_terms_kernel.
-template <int VEC>
-__global__ void __launch_bounds__(TRAIN_THREADS, 2)
-    align_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial,
-                      unsigned* __restrict__ ticket, int B, int P, int HW, float eps, float grad_scale) {
-    constexpr int L = 32 / VEC;
-    constexpr int U = VEC == 4 ? 2 : 4;  // channels in flight per thread and view
-    __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
-    __shared__ float s_col[TRAIN_TILE];
-    const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
-    const int b = blockIdx.y, hw0 = blockIdx.x * TRAIN_TILE + hwl * VEC;
-    if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) *ticket = 0u;  // for loss_terms_kernel, the next launch of the stream
-    const bool ok = hw0 < HW;
-    const size_t img = static_cast<size_t>(P) * HW;
-    const size_t off1 = static_cast<size_t>(b) * img + hw0, off2 = off1 + static_cast<size_t>(B) * img;
-    const float* p1 = pf + off1;
-    const float* p2 = pf + off2;
-    float acc[VEC];
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
-    if (ok) {
-        int c = cg;
-        for (; c + (U - 1) * CG < P; c += U * CG) {
-            float a[U][VEC], v[U][VEC];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
-                ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[u][k], v[u][k], acc[k]);
-        }
-        for (; c < P; c += CG) {
-            float a[VEC], v[VEC];
-            ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
-            ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[k], v[k], acc[k]);
-        }
-    }
-    tile_reduce<VEC, false>(acc, s_red, s_col);
-    if (tid < TRAIN_TILE) {  // warp 0: lane = position of the tile
-        const bool valid = blockIdx.x * TRAIN_TILE + tid < HW;
-        const float d = s_col[tid] + eps;
-        s_col[tid] = valid ? grad_scale / d : 0.f;
-        const float l = warp_sum(valid ? -logf(d) : 0.f);
-        if (tid == 0) partial[static_cast<size_t>(b) * gridDim.x + blockIdx.x] = l;
-    }
-    if (grad == nullptr) return;
-    __syncthreads();
-    if (!ok) return;
-    float kf[VEC];
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) kf[k] = s_col[hwl * VEC + k];
-    float* g1 = grad + off1;
-    float* g2 = grad + off2;
-    int c = cg;
-    for (; c + (U - 1) * CG < P; c += U * CG) {
-        float a[U][VEC], v[U][VEC];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
-            ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) {
-                const float t = a[u][k];
-                a[u][k] = kf[k] * v[u][k];
-                v[u][k] = kf[k] * t;
-            }
-            stv_cs<VEC>(g1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
-            stv_cs<VEC>(g2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
-        }
-    }
-    for (; c < P; c += CG) {
-        float a[VEC], v[VEC];
-        ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
-        ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
-#pragma unroll
-        for (int k = 0; k < VEC; ++k) {
-            const float t = a[k];
-            a[k] = kf[k] * v[k];
-            v[k] = kf[k] * t;
-        }
-        stv_cs<VEC>(g1 + static_cast<size_t>(c) * HW, a);
-        stv_cs<VEC>(g2 + static_cast<size_t>(c) * HW, v);
-    }
-}
-
-// ---- tanh loss, classification loss, weighting: ONE launch ------------------------------------------------------------
-// loss_terms_kernel: grid = 2 * ceil(P / 128) tanh CTAs + (pretrain ? 0 : 2B) classification CTAs, 128 threads each; the
-// CTA that takes the last ticket sums every partial array in a fixed order and writes result[8] (so the values do not
-// depend on which CTA that is). The ticket is zeroed by align_loss_kernel, which the stream runs before this kernel.
+// ---- tanh loss, classification loss, weighting: extra CTAs of the map kernel -------------------------------------------
+// The first n_terms = 2 * ceil(P / 128) (tanh) + (pretrain ? 0 : 2B) (classification) CTAs of pipnet_loss_kernel do these
+// terms on their first 128 threads while the other CTAs stream the map; every CTA takes a ticket after publishing its
+// partials and the one that takes the last sums every partial array in a fixed order and writes result[8] (so the values
+// do not depend on which CTA that is). The ticket is zeroed by a 4-byte memset node ahead of the kernel.
+__device__ __forceinline__ void bar128() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 struct ValIdx {
     float v;
     int i;
@@ -206,7 +110,7 @@ struct LossTermsArgs {
     const float* mult;        // [1]
     float* grad_pooled;       // [2B, P] or null
     float* grad_out;          // [2B, K] or null
-    const float* align_partial;  // [n_align], written by align_loss_kernel
+    const float* align_partial;  // [n_align], written by the map CTAs
     float* tanh_partial;      // [2 * tanh_blocks]
     float* row_loss;          // [2B]
     float* row_gmult;         // [2B]
@@ -246,7 +150,7 @@ __device__ __forceinline__ void tanh_terms(const LossTermsArgs& a, int view, int
     }
     l = warp_sum(l);
     if ((threadIdx.x & 31) == 0) s_f[threadIdx.x >> 5] = l;
-    __syncthreads();
+    bar128();
     if (threadIdx.x == 0) a.tanh_partial[view * a.tanh_blocks + pblock] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
 }
 
@@ -275,19 +179,19 @@ __device__ __forceinline__ void class_terms(const LossTermsArgs& a, int i, float
         s_f[warp] = vmax;
         s_vi[warp] = best;
     }
-    __syncthreads();
+    bar128();
     vmax = fmaxf(fmaxf(s_f[0], s_f[1]), fmaxf(s_f[2], s_f[3]));
     best = better(better(s_vi[0], s_vi[1]), better(s_vi[2], s_vi[3]));
-    __syncthreads();
+    bar128();
 
     float se = 0.f;
     for (int k = tid; k < K; k += 128) se += expf(value(o[k]) - vmax);
     se = warp_sum(se);
     if (lane == 0) s_f[warp] = se;
-    __syncthreads();
+    bar128();
     se = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
     const float lse = vmax + logf(se);
-    __syncthreads();
+    bar128();
 
     float gm = 0.f;
     if (a.grad_out != nullptr) {
@@ -309,7 +213,7 @@ __device__ __forceinline__ void class_terms(const LossTermsArgs& a, int i, float
     }
     gm = warp_sum(gm);
     if (lane == 0) s_f[warp] = gm;
-    __syncthreads();
+    bar128();
     if (tid == 0) {
         a.row_loss[i] = (y >= 0 && y < K) ? lse - value(o[y]) : 0.f;
         a.row_gmult[i] = (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
@@ -323,9 +227,9 @@ __device__ __forceinline__ float block_sum_128(const float* v, int n, float* s_f
     float acc = 0.f;
     for (int i = threadIdx.x; i < n; i += 128) acc += __ldcg(v + i);
     acc = warp_sum(acc);
-    __syncthreads();  // s_f may still be read from the previous call
+    bar128();  // s_f may still be read from the previous call
     if ((threadIdx.x & 31) == 0) s_f[threadIdx.x >> 5] = acc;
-    __syncthreads();
+    bar128();
     return (s_f[0] + s_f[1]) + (s_f[2] + s_f[3]);
 }
 
@@ -357,24 +261,135 @@ __device__ __forceinline__ void finalize_terms(const LossTermsArgs& a, float* s_
     }
 }
 
-__global__ void __launch_bounds__(128) loss_terms_kernel(const LossTermsArgs a) {
+// The CTAs that do these terms, and the CTA that takes the last ticket, run them on their first 128 threads.
+__device__ __forceinline__ void loss_terms_cta(const LossTermsArgs& a, int idx, float* s_f, ValIdx* s_vi) {
+    const int n_tanh = 2 * a.tanh_blocks;
+    if (idx < n_tanh)
+        tanh_terms(a, idx / a.tanh_blocks, idx % a.tanh_blocks, s_f);
+    else
+        class_terms(a, idx - n_tanh, s_f, s_vi);
+}
+
+// ---- align loss -----------------------------------------------------------------------------------------------------
+// pf [2B, P, HW]: view 1 = images [0, B), view 2 = images [B, 2B). For patch n = (b, hw): d_n = sum_c pf1 * pf2,
+// loss = -mean_n log(d_n + eps) (the two directions of train.py:173 have the same value); d loss / d pf1 = grad_scale *
+// pf2 / (d_n + eps) and the mirror image for pf2, grad_scale = -align_weight / (2 N).
+// grid = n_terms + ceil(HW / 32) * B CTAs (the small-terms CTAs first, so that they start with the first wave), block =
+// (32 / VEC) * channel groups, at least 128. partial [B * tiles] = per-CTA sum of -log(d + eps).
+template <int VEC>
+__global__ void __launch_bounds__(TRAIN_THREADS, 2)
+    pipnet_loss_kernel(const float* __restrict__ pf, float* __restrict__ grad, float* __restrict__ partial, int n_terms,
+                       int tiles, int B, int P, int HW, float eps, float grad_scale, const LossTermsArgs terms) {
     __shared__ float s_f[4];
     __shared__ ValIdx s_vi[4];
     __shared__ int s_last;
-    const int n_tanh = 2 * a.tanh_blocks;
-    if (static_cast<int>(blockIdx.x) < n_tanh)
-        tanh_terms(a, blockIdx.x / a.tanh_blocks, blockIdx.x % a.tanh_blocks, s_f);
-    else
-        class_terms(a, blockIdx.x - n_tanh, s_f, s_vi);
-    // both roles end with thread 0 writing this CTA's partials: publish them, then take a ticket
-    if (threadIdx.x == 0) {
-        __threadfence();
-        s_last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
+    if (static_cast<int>(blockIdx.x) < n_terms) {
+        if (threadIdx.x >= 128) return;
+        loss_terms_cta(terms, blockIdx.x, s_f, s_vi);
+        if (threadIdx.x == 0) {  // both roles end with thread 0 writing this CTA's partials: publish them, take a ticket
+            __threadfence();
+            s_last = atomicAdd(terms.ticket, 1u) == gridDim.x - 1;
+        }
+        bar128();
+        if (s_last) {
+            __threadfence();
+            finalize_terms(terms, s_f);
+        }
+        return;
+    }
+    constexpr int L = 32 / VEC;
+    constexpr int U = VEC == 4 ? 2 : 4;  // channels in flight per thread and view
+    __shared__ float s_red[TRAIN_THREADS / 32][TRAIN_TILE + 1];
+    __shared__ float s_col[TRAIN_TILE];
+    const int tid = threadIdx.x, hwl = tid % L, cg = tid / L, CG = blockDim.x / L;
+    const int map_cta = blockIdx.x - n_terms, tile = map_cta % tiles, b = map_cta / tiles;
+    const int hw0 = tile * TRAIN_TILE + hwl * VEC;
+    const bool ok = hw0 < HW;
+    const size_t img = static_cast<size_t>(P) * HW;
+    const size_t off1 = static_cast<size_t>(b) * img + hw0, off2 = off1 + static_cast<size_t>(B) * img;
+    const float* p1 = pf + off1;
+    const float* p2 = pf + off2;
+    float acc[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
+    if (ok) {
+        int c = cg;
+        for (; c + (U - 1) * CG < P; c += U * CG) {
+            float a[U][VEC], v[U][VEC];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+                ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[u][k], v[u][k], acc[k]);
+        }
+        for (; c < P; c += CG) {
+            float a[VEC], v[VEC];
+            ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+            ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(a[k], v[k], acc[k]);
+        }
+    }
+    tile_reduce<VEC, false>(acc, s_red, s_col);
+    if (tid < TRAIN_TILE) {  // warp 0: lane = position of the tile
+        const bool valid = tile * TRAIN_TILE + tid < HW;
+        const float d = s_col[tid] + eps;
+        s_col[tid] = valid ? grad_scale / d : 0.f;
+        const float l = warp_sum(valid ? -logf(d) : 0.f);
+        if (tid == 0) {
+            partial[static_cast<size_t>(b) * tiles + tile] = l;
+            __threadfence();
+            s_last = atomicAdd(terms.ticket, 1u) == gridDim.x - 1;
+        }
     }
     __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    finalize_terms(a, s_f);
+    if (s_last && tid < 128) {  // no barrier of the whole CTA follows: the other threads go on to the gradient pass
+        __threadfence();
+        finalize_terms(terms, s_f);
+    }
+    if (grad == nullptr || !ok) return;
+    float kf[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) kf[k] = s_col[hwl * VEC + k];
+    float* g1 = grad + off1;
+    float* g2 = grad + off2;
+    int c = cg;
+    for (; c + (U - 1) * CG < P; c += U * CG) {
+        float a[U][VEC], v[U][VEC];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+            ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) {
+                const float t = a[u][k];
+                a[u][k] = kf[k] * v[u][k];
+                v[u][k] = kf[k] * t;
+            }
+            stv_cs<VEC>(g1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
+            stv_cs<VEC>(g2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
+        }
+    }
+    for (; c < P; c += CG) {
+        float a[VEC], v[VEC];
+        ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
+        ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const float t = a[k];
+            a[k] = kf[k] * v[k];
+            v[k] = kf[k] * t;
+        }
+        stv_cs<VEC>(g1 + static_cast<size_t>(c) * HW, a);
+        stv_cs<VEC>(g2 + static_cast<size_t>(c) * HW, v);
+    }
 }
 
 // buf *= *scale unless *scale == 1 (the usual loss.backward() case costs one tiny launch and no pass over memory).
