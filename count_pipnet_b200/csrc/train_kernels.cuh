@@ -357,13 +357,15 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
     for (int k = 0; k < VEC; ++k) kf[k] = s_col[hwl * VEC + k];
     float* g1 = grad + off1;
     float* g2 = grad + off2;
-    int c = cg;
-    for (; c + (U - 1) * CG < P; c += U * CG) {
+    // second pass from the LAST channel row down: what the first pass read most recently is what L2 still holds
+    if (cg >= P) return;
+    int c = cg + (P - 1 - cg) / CG * CG;  // this thread's last row
+    for (; c - (U - 1) * CG >= cg; c -= U * CG) {
         float a[U][VEC], v[U][VEC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            ldv<VEC>(p1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
-            ldv<VEC>(p2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
+            ldv<VEC>(p1 + static_cast<size_t>(c - u * CG) * HW, a[u]);
+            ldv<VEC>(p2 + static_cast<size_t>(c - u * CG) * HW, v[u]);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -373,11 +375,11 @@ __global__ void __launch_bounds__(TRAIN_THREADS, 2)
                 a[u][k] = kf[k] * v[u][k];
                 v[u][k] = kf[k] * t;
             }
-            stv_cs<VEC>(g1 + static_cast<size_t>(c + u * CG) * HW, a[u]);
-            stv_cs<VEC>(g2 + static_cast<size_t>(c + u * CG) * HW, v[u]);
+            stv_cs<VEC>(g1 + static_cast<size_t>(c - u * CG) * HW, a[u]);
+            stv_cs<VEC>(g2 + static_cast<size_t>(c - u * CG) * HW, v[u]);
         }
     }
-    for (; c < P; c += CG) {
+    for (; c >= cg; c -= CG) {
         float a[VEC], v[VEC];
         ldv<VEC>(p1 + static_cast<size_t>(c) * HW, a);
         ldv<VEC>(p2 + static_cast<size_t>(c) * HW, v);
