@@ -131,3 +131,44 @@ def test_train_pipnet_epoch_on_cpu(pretrain, finetune, capsys):
     else:
         assert float(net._classification.normalization_multiplier) >= 1.0   # train.py:136 clamp
         assert float(net._classification.weight.min()) >= 0.0
+
+
+class _FakeCudaMap:
+    """Stands in for a CUDA feature map in engine.use_train_head, which only looks at these three properties."""
+    is_cuda = True
+    dtype = torch.float32
+
+    def dim(self):
+        return 4
+
+
+def test_use_train_head_decisions(capsys):
+    """Which autograd forwards hand their head to the training kernels: plain nn.Softmax(dim=1) add-ons with the stock
+    max pool (PIP-Net) or the spatial sum (Count-PIP-Net); never the Gumbel activation, never CPU tensors."""
+    import torch.nn as nn
+    from count_pipnet_b200 import engine, synth
+    from count_pipnet_b200.pipnet import count_pipnet as my_count
+    from count_pipnet_b200.pipnet import pipnet as my_pipnet
+    pip, _ = my_pipnet.get_pipnet(5, synth.make_args(use_mid_layers=True, num_stages=1))
+    pip_addon, _ = my_pipnet.get_pipnet(5, synth.make_args(num_features=8, use_mid_layers=True, num_stages=1))
+    cnt_soft, _ = my_count.get_count_network(5, synth.make_args(num_features=8, use_mid_layers=True, num_stages=1,
+                                                                activation="softmax"))
+    cnt_gumbel, _ = my_count.get_count_network(5, synth.make_args(num_features=8, use_mid_layers=True, num_stages=1,
+                                                                  activation="gumbel_softmax"))
+    capsys.readouterr()
+    fake = _FakeCudaMap()
+    assert engine.use_train_head(pip, fake, want_max=True)
+    assert engine.use_train_head(pip_addon, fake, want_max=True)
+    assert engine.use_train_head(cnt_soft, fake, want_max=False)
+    assert not engine.use_train_head(cnt_gumbel, fake, want_max=False)
+    assert not engine.use_train_head(pip, torch.zeros(1, 4, 2, 2), want_max=True)          # CPU tensor
+    pip._pool = nn.Sequential(nn.AdaptiveAvgPool2d((1, 1)), nn.Flatten())                   # not the stock pool
+    assert not engine.use_train_head(pip, fake, want_max=True)
+    pip_addon._add_on[-1].dim = 2                                                            # softmax over another axis
+    assert not engine.use_train_head(pip_addon, fake, want_max=True)
+    old = engine.TRAIN_KERNELS
+    try:
+        engine.TRAIN_KERNELS = False
+        assert not engine.use_train_head(cnt_soft, fake, want_max=False)
+    finally:
+        engine.TRAIN_KERNELS = old
